@@ -1,0 +1,205 @@
+/*
+ * rt_b200.h — C ABI of the B200-native ray-scene kernel.
+ *
+ * Drop-in boundary for ONE hot path of blubs/OpenGLRaytracer: the per-pixel
+ * compute shader raytrace_compute.glsl and the five host lines that launch it
+ * (main.cpp:220-238: glUseProgram / glBindImageTexture(RGBA8) / glUniform1f(time)
+ * / glDispatchCompute(W,H,1) / glFinish).  The reference has no FFI; the structs
+ * below mirror the shader's own structs field-for-field so that a maintainer can
+ * replace the GL dispatch by one call.
+ *
+ * Citation shorthand: glsl:N = OpenGLRaytracer/raytrace_compute.glsl line N,
+ * main.cpp:N = OpenGLRaytracer/main.cpp line N.
+ *
+ * All structs are plain-old-data, tightly packed 4-byte words.  No torch types,
+ * no C++ types.  Every entry point returns RT_OK (0) or a negative rt_status;
+ * nothing ever calls exit() (the reference's only error path, main.cpp:50-53).
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* Limits.  The reference's stack machine holds 100 frames (glsl:873-874) and its
+ * runaway guard trips after 10001 loop iterations (glsl:1076-1101); we accept
+ * depth 0..RT_MAX_DEPTH and reproduce the in-band red pixel when the guard would
+ * have tripped.  */
+#define RT_MAX_DEPTH   15
+#define RT_MAX_LIGHTS  64
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_BAD_ARG = -1,      /* null pointer, non-positive size, depth out of range ... */
+    RT_ERR_CUDA = -2,         /* a CUDA runtime call failed; see rt_last_error_string() */
+    RT_ERR_NO_DEVICE = -3,    /* no CUDA device / kernel image not loadable (no CPU fallback) */
+    RT_ERR_NOMEM = -4,
+    RT_ERR_UNSUPPORTED = -5
+} rt_status;
+
+/* glsl:56-69 `struct Material` (20 words). */
+typedef struct rt_material {
+    float ambient[4];
+    float diffuse[4];
+    float specular[4];
+    float shininess;
+    float emissive[4];
+    float reflectivity;
+    float transparency;
+    float refraction_index;
+} rt_material;
+
+/* glsl:244-258 `struct Object` with glsl:166-175 Box/Sphere inlined (33 words).
+ * Null conventions as in the shader (glsl:178-179, 749, 759): an object is a box
+ * iff (box_mins,box_maxs) != all-zero; else a sphere iff sphere_radius != -1;
+ * else it is skipped. */
+typedef struct rt_object {
+    float box_mins[3];
+    float box_maxs[3];
+    float sphere_radius;
+    float position[3];
+    float angles[3];          /* pitch, yaw, roll in degrees (glsl:492-503) */
+    rt_material material;
+} rt_object;
+
+/* glsl:190-196 `struct Light` (15 words). */
+typedef struct rt_light {
+    float position[3];
+    float ambient[4];
+    float diffuse[4];
+    float specular[4];
+} rt_light;
+
+/* The shader's global scene: objects[] + objects_count (glsl:261-321),
+ * lights[] + lights_count (glsl:199-224), MAX_RAYTRACE_DEPTH (glsl:22). */
+typedef struct rt_scene {
+    const rt_object* objects;
+    int32_t objects_count;
+    const rt_light* lights;
+    int32_t lights_count;
+    int32_t max_depth;
+} rt_scene;
+
+/* glsl:36-50 `struct Camera` (10 words); the "camera uniforms". */
+typedef struct rt_camera {
+    float position[3];
+    float angles[3];          /* pitch, yaw, roll in degrees */
+    float v_fov;
+    float aspect;
+    float near_plane;
+    float far_plane;
+} rt_camera;
+
+/* Counters filled when rt_options.stats != NULL (instrumented twin kernel). A
+ * "ray" is one get_closest_collision() invocation of the reference (glsl:738):
+ * primary + reflection + refraction + shadow rays. */
+typedef struct rt_stats {
+    uint64_t rays;            /* get_closest_collision calls the reference would make */
+    uint64_t nodes;           /* bounce-tree nodes (primary+reflection+refraction rays) */
+    uint64_t hit_nodes;       /* nodes whose ray hit something */
+    uint64_t shadow_rays;
+    uint64_t box_tests;       /* ray/box slab tests actually executed on the device */
+    uint64_t sphere_tests;    /* ray/sphere tests actually executed on the device */
+    uint64_t red_pixels;      /* samples that tripped the runaway guard (glsl:1098) */
+    float kernel_ms;          /* CUDA-event time of the render kernel(s) of this call */
+    float total_ms;           /* CUDA-event time incl. uploads and the D2H copy */
+} rt_stats;
+
+/* Extended options; zero-initialise then override (rt_options_default()). The
+ * defaults reproduce the shader exactly: 1 sample at the integer pixel corner
+ * (glsl:377-378), whole image, host output, synchronous. */
+typedef struct rt_options {
+    int32_t spp;              /* samples per pixel; 1 = reference behaviour; n*n stratified jitter otherwise */
+    uint32_t seed;            /* jitter hash seed (ignored when spp == 1) */
+    int32_t y0, y1;           /* row band [y0,y1) to render; y1 <= 0 means height */
+    int32_t out_is_device;    /* out_rgba is a device pointer on `device` (no D2H copy) */
+    int32_t out_band_only;    /* out_rgba holds only rows [y0,y1) (band-local), else the full image */
+    int32_t device;           /* CUDA device ordinal; -1 = current device */
+    int32_t strict;           /* 1 = strict-arithmetic kernel (-fmad=false, IEEE divides, shader op order) */
+    int32_t async;            /* 1 = do not synchronise (device output only); pair with rt_synchronize() */
+    void* stream;             /* cudaStream_t to launch on; NULL = the context's own stream */
+    rt_stats* stats;          /* optional counters/timings */
+} rt_options;
+
+typedef struct rt_context rt_context;
+
+/* Library/ABI introspection. */
+int rt_abi_version(void);
+const char* rt_last_error_string(void);
+/* Number of kernels this library has launched in this process (bench evidence). */
+uint64_t rt_kernel_launch_count(void);
+
+/* Context: owns device buffers, a stream and pinned staging on one device.
+ * Replaces the GL context + texture object (main.cpp:47-76, 152-159). */
+int rt_create(rt_context** out_ctx, int device);
+int rt_destroy(rt_context* ctx);
+int rt_synchronize(rt_context* ctx);
+
+void rt_options_default(rt_options* opts);
+
+/* THE drop-in call (north_star): render(scene, camera_uniforms, out_rgba, w, h).
+ * Replaces glUseProgram+glBindImageTexture+glUniform1f+glDispatchCompute+glFinish
+ * (main.cpp:220-238).  out_rgba: caller-owned host buffer of width*height*4
+ * bytes, R,G,B,A tightly packed, row 0 = bottom scanline (GL order), A = 0
+ * (glsl:404).  Synchronous like glFinish().  Uses a lazily created default
+ * context on the current device. */
+int rt_render(const rt_scene* scene, const rt_camera* camera_uniforms,
+              uint8_t* out_rgba, int width, int height);
+
+/* Extended call: explicit context and options (spp, row band, device output). */
+int rt_render_ex(rt_context* ctx, const rt_scene* scene, const rt_camera* camera_uniforms,
+                 void* out_rgba, int width, int height, const rt_options* opts);
+
+/* Throughput mode (BASELINE config 5): n_frames cameras over one scene in ONE
+ * launch; frame k is written at out_rgba + k*width*height*4. */
+int rt_render_batch(rt_context* ctx, const rt_scene* scene, const rt_camera* cameras,
+                    int n_frames, void* out_rgba, int width, int height, const rt_options* opts);
+
+/* Two-phase use for steady-state rendering of a fixed scene: upload once
+ * (host prologue: per-object matrices, glsl:650-652, 718), render many. */
+int rt_upload_scene(rt_context* ctx, const rt_scene* scene);
+int rt_render_uploaded(rt_context* ctx, const rt_camera* cameras, int n_frames,
+                       void* out_rgba, int width, int height, const rt_options* opts);
+
+/* The shader's hard-coded data as a function of its one real uniform `time`
+ * (glsl:4): objects (glsl:261-321), lights (glsl:199-224), camera (glsl:334-364).
+ * objects must have room for 5 rt_object, lights for 3 rt_light.  scene->max_depth
+ * is set to the shipped MAX_RAYTRACE_DEPTH = 0 (glsl:22). */
+int rt_builtin_scene(float time, rt_object* objects5, rt_light* lights3, rt_scene* scene);
+int rt_builtin_camera(float time, rt_camera* camera);
+/* Orbit camera from the shader's `speed` variable directly (glsl:343-358); used
+ * by the turntable batch (config 5). */
+int rt_orbit_camera(float speed, rt_camera* camera);
+
+/* Scaled synthetic scene (BASELINE config 4; generator defined in SURVEY §8d):
+ * object 0 is the builtin enclosing cube, objects 1..n-1 are oriented boxes
+ * (spheres when i%5==4) placed by splitmix64(seed).  objects must hold n
+ * rt_object, lights 3 rt_light. */
+int rt_scaled_scene(int n_objects, uint64_t seed, rt_object* objects, rt_light* lights3, rt_scene* scene);
+
+/* Replaces the draw_screen_vert/frag blit (main.cpp:240-260): binary PPM (P6),
+ * rows flipped so the picture is upright, alpha dropped (frag:9). */
+int rt_write_ppm(const char* path, const uint8_t* rgba, int width, int height);
+int rt_write_raw(const char* path, const uint8_t* rgba, int width, int height);
+
+/* Microbenchmark: dependent-free FP32 FMA chains on every SM; returns measured
+ * TFLOP/s (2 flop per FMA).  Denominator check for the FP32 roofline. */
+int rt_fp32_peak_tflops(int device, int iters, double* tflops, float* ms);
+
+/* Multi-GPU helper for the fused gather: export/import a CUDA IPC handle of a
+ * device framebuffer so that other ranks' kernels store their row band directly
+ * into rank 0's buffer over NVLink. handle is 64 bytes. */
+int rt_ipc_export(void* device_ptr, uint8_t handle64[64]);
+int rt_ipc_import(const uint8_t handle64[64], void** device_ptr);
+int rt_ipc_close(void* device_ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */
