@@ -143,6 +143,11 @@ int rt_synchronize(rt_context* ctx);
 
 void rt_options_default(rt_options* opts);
 
+/* Page-locked host memory for out_rgba: lets the device->host copy of the frame
+ * run at full PCIe rate (a pageable buffer works too, only slower). */
+int rt_host_alloc(void** ptr, size_t bytes);
+int rt_host_free(void* ptr);
+
 /* THE drop-in call (north_star): render(scene, camera_uniforms, out_rgba, w, h).
  * Replaces glUseProgram+glBindImageTexture+glUniform1f+glDispatchCompute+glFinish
  * (main.cpp:220-238).  out_rgba: caller-owned host buffer of width*height*4

@@ -1,0 +1,91 @@
+/*
+ * rt_device.h — device-side data layout shared by the host prologue (rt_host.cpp)
+ * and the kernels (rt_kernel.cuh).
+ *
+ * HBM layout (everything is tiny next to 180 GB; what matters is the split):
+ *   HOT  — what the brute-force loop (glsl:744-779) touches for EVERY (ray,
+ *          object) pair.  Stored as dense float4 arrays, boxes and spheres in
+ *          separate lists (each in original object order), so that a warp
+ *          reads one record with 3 (fast) / 5 (strict) broadcast 16-byte loads
+ *          from shared memory.
+ *   COLD — what only the single closest hit of a ray needs (matrices for the
+ *          hit point / normal, glsl:718-721, and the material, glsl:791).
+ *          One 256-byte record per original object, read once per ray.
+ */
+#ifndef RT_DEVICE_H
+#define RT_DEVICE_H
+
+#include <stdint.h>
+
+/* same value as RT_MAX_DEPTH in include/rt_b200.h (checked in rt_host.cpp) */
+#define RT_MAX_DEPTH_DEV 15
+
+#define RT_KIND_SKIP   0
+#define RT_KIND_BOX    1
+#define RT_KIND_SPHERE 2
+
+/* float4 per box in the hot list */
+#define RT_BOX_F4_FAST   3   /* rows of the recentred, 1/half-extent-scaled world->local map */
+#define RT_BOX_F4_STRICT 5   /* world->local rows (3) + (mins.xyz, maxs.x) + (maxs.y, maxs.z, 0, 0) */
+
+/* Cold record: 64 words. */
+struct RtCold {
+    float w2l[12];      /* world->local rows: row i = (m[0][i], m[1][i], m[2][i], m[3][i]) of inverse(T*R), glsl:652 */
+    float l2w[12];      /* local->world rows, glsl:650 */
+    float nmat[9];      /* transpose(inverse(mat3(l2w))), column-major c[col][row], glsl:718 */
+    float mins[3];
+    float maxs[3];
+    int32_t kind;
+    int32_t hot_index;  /* index in the box / sphere hot list */
+    /* material (glsl:56-69) */
+    float ambient[4];
+    float diffuse[4];
+    float specular[4];
+    float emissive[4];
+    float shininess;
+    float reflectivity;
+    float transparency;
+    float refraction_index;
+    float position[3];  /* sphere centre */
+};
+
+struct RtLightDev {
+    float position[4];
+    float ambient[4];
+    float diffuse[4];
+    float specular[4];
+};
+
+/* Per-frame camera uniforms after the host prologue: inverse(proj*view)
+ * (glsl:383, pixel-invariant) and the ray origin (glsl:391). */
+struct RtCameraDev {
+    float inv_pv[16];   /* column-major c[col][row] */
+    float position[4];
+};
+
+struct RtCounters {
+    unsigned long long rays, nodes, hit_nodes, shadow_rays, box_tests, sphere_tests, red_pixels, pad;
+};
+
+struct RtParams {
+    const float4* box_hot;
+    const float4* sph_hot;      /* (cx, cy, cz, r*r) */
+    const int32_t* box_obj;     /* hot index -> original object index */
+    const int32_t* sph_obj;
+    const RtCold* cold;
+    const RtLightDev* lights;
+    const RtCameraDev* cams;
+    uint8_t* out;               /* frame k at out + k*frame_stride */
+    RtCounters* counters;       /* used by the instrumented twin only */
+    long long frame_stride;     /* bytes */
+    int32_t n_box, n_sph, n_lights, max_depth;
+    int32_t n_frames, width, height, y0, y1;
+    int32_t out_row0;           /* image row stored at out row 0 (y0 for band-only output, else 0) */
+    int32_t spp, spp_n;         /* spp_n = sqrt(spp) if spp is a perfect square, else 0 */
+    uint32_t seed;
+    int32_t tiles_x, tiles_y;   /* 8x4-pixel warp tiles covering width x (y1-y0) */
+    int32_t resident;           /* 1: whole hot scene staged in shared memory once per CTA */
+    int32_t stream_tile;        /* boxes per streamed tile (streaming mode) */
+};
+
+#endif

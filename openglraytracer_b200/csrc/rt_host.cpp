@@ -1,0 +1,488 @@
+/*
+ * rt_host.cpp — headless host side of the C ABI (include/rt_b200.h).
+ *
+ * Replaces the reference's GL host path for the hot path only: context +
+ * texture (main.cpp:47-76, 152-159) -> rt_context with device buffers;
+ * glUniform1f/glDispatchCompute/glFinish (main.cpp:220-238) -> rt_render*.
+ * The host prologue hoists what the shader recomputes per pixel / per test:
+ * inverse(proj*view) (glsl:366-383) once per frame, the box transforms
+ * (glsl:650-652, 718) once per object.
+ *
+ * No CPU fallback: without a usable CUDA device every render call fails with
+ * RT_ERR_NO_DEVICE / RT_ERR_CUDA.
+ */
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "rt_device.h"
+#include "rt_hostmath.h"
+
+static_assert(RT_MAX_DEPTH == RT_MAX_DEPTH_DEV, "depth limits out of sync");
+static_assert(sizeof(rt_material) == 20 * 4, "rt_material must be 20 words (glsl:56-69)");
+static_assert(sizeof(rt_object) == 33 * 4, "rt_object must be 33 words (glsl:244-258)");
+static_assert(sizeof(rt_light) == 15 * 4, "rt_light must be 15 words (glsl:190-196)");
+static_assert(sizeof(rt_camera) == 10 * 4, "rt_camera must be 10 words (glsl:36-50)");
+static_assert(sizeof(RtCold) == 64 * 4, "cold record must be 256 bytes");
+
+namespace rt_fast {
+cudaError_t launch(const RtParams& P, int grid, bool count, cudaStream_t stream);
+cudaError_t configure(int device, int* max_smem_optin);
+}
+namespace rt_strict {
+cudaError_t launch(const RtParams& P, int grid, bool count, cudaStream_t stream);
+cudaError_t configure(int device, int* max_smem_optin);
+}
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ||   \
+                                e_ == cudaErrorNoKernelImageForDevice                     \
+                            ? RT_ERR_NO_DEVICE                                            \
+                            : RT_ERR_CUDA,                                                \
+                        "%s failed: %s", #call, cudaGetErrorString(e_));                  \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;   // elements
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 4 + 16;
+        cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct HostScene {
+    std::vector<float> box_fast, box_strict;   // float4 records
+    std::vector<float> sph;                    // (c, r*r)
+    std::vector<int32_t> box_obj, sph_obj;
+    std::vector<RtCold> cold;
+    std::vector<RtLightDev> lights;
+    int max_depth = 0;
+};
+
+}  // namespace
+
+struct rt_context {
+    int device = 0;
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    DevBuf<float> d_box_fast, d_box_strict, d_sph;
+    DevBuf<int32_t> d_box_obj, d_sph_obj;
+    DevBuf<RtCold> d_cold;
+    DevBuf<RtLightDev> d_lights;
+    DevBuf<RtCameraDev> d_cams;
+    DevBuf<uint8_t> d_out;
+    DevBuf<RtCounters> d_cnt;
+    uint8_t* h_pinned = nullptr;
+    size_t h_pinned_cap = 0;
+    // uploaded scene
+    bool have_scene = false;
+    int n_box = 0, n_sph = 0, n_lights = 0, max_depth = 0;
+};
+
+namespace {
+
+bool is_box(const rt_object& o) {   // glsl:749: box != null_box
+    return !(o.box_mins[0] == 0.0f && o.box_mins[1] == 0.0f && o.box_mins[2] == 0.0f &&
+             o.box_maxs[0] == 0.0f && o.box_maxs[1] == 0.0f && o.box_maxs[2] == 0.0f);
+}
+
+// Host prologue: per-object matrices and the hot/cold split.
+int build_host_scene(const rt_scene* scene, HostScene* hs) {
+    const int n = scene->objects_count;
+    hs->cold.resize(n > 0 ? n : 0);
+    hs->max_depth = scene->max_depth;
+    for (int i = 0; i < n; i++) {
+        const rt_object& o = scene->objects[i];
+        RtCold& c = hs->cold[i];
+        memset(&c, 0, sizeof(c));
+        memcpy(c.ambient, o.material.ambient, 16);
+        memcpy(c.diffuse, o.material.diffuse, 16);
+        memcpy(c.specular, o.material.specular, 16);
+        memcpy(c.emissive, o.material.emissive, 16);
+        c.shininess = o.material.shininess;
+        c.reflectivity = o.material.reflectivity;
+        c.transparency = o.material.transparency;
+        c.refraction_index = o.material.refraction_index;
+        memcpy(c.position, o.position, 12);
+        memcpy(c.mins, o.box_mins, 12);
+        memcpy(c.maxs, o.box_maxs, 12);
+        if (is_box(o)) {
+            float l2w[16], w2l[16];
+            rthm::transform(o.position, o.angles, l2w);     // glsl:650
+            rthm::inverse4(l2w, w2l);                       // glsl:652
+            rthm::normal_matrix(l2w, c.nmat);               // glsl:718
+            for (int r = 0; r < 3; r++)
+                for (int k = 0; k < 4; k++) {
+                    c.w2l[4 * r + k] = rthm::at(w2l, r, k);
+                    c.l2w[4 * r + k] = rthm::at(l2w, r, k);
+                }
+            // A slab of zero thickness can never satisfy t_near < t_far (glsl:680): never hit.
+            const bool degenerate = o.box_mins[0] == o.box_maxs[0] || o.box_mins[1] == o.box_maxs[1] ||
+                                    o.box_mins[2] == o.box_maxs[2];
+            // strict record (always built so both kernels see the same object set, modulo degenerate)
+            c.kind = RT_KIND_BOX;
+            c.hot_index = (int32_t)hs->box_obj.size();
+            hs->box_obj.push_back(i);
+            for (int r = 0; r < 3; r++)
+                for (int k = 0; k < 4; k++) hs->box_strict.push_back(c.w2l[4 * r + k]);
+            hs->box_strict.push_back(o.box_mins[0]); hs->box_strict.push_back(o.box_mins[1]);
+            hs->box_strict.push_back(o.box_mins[2]); hs->box_strict.push_back(o.box_maxs[0]);
+            hs->box_strict.push_back(o.box_maxs[1]); hs->box_strict.push_back(o.box_maxs[2]);
+            hs->box_strict.push_back(0.0f); hs->box_strict.push_back(0.0f);
+            // fast record: rows of diag(1/h) * (w2l - centre), h = half extent (double for accuracy).
+            for (int r = 0; r < 3; r++) {
+                const double h = 0.5 * ((double)o.box_maxs[r] - (double)o.box_mins[r]);
+                const double ctr = 0.5 * ((double)o.box_maxs[r] + (double)o.box_mins[r]);
+                if (degenerate) {
+                    // unreachable slab: local'' origin far outside, direction row zero -> always a miss
+                    hs->box_fast.push_back(0.0f); hs->box_fast.push_back(0.0f); hs->box_fast.push_back(0.0f);
+                    hs->box_fast.push_back(4.0f);
+                } else {
+                    const double ih = 1.0 / h;
+                    for (int k = 0; k < 3; k++) hs->box_fast.push_back((float)((double)c.w2l[4 * r + k] * ih));
+                    hs->box_fast.push_back((float)(((double)c.w2l[4 * r + 3] - ctr) * ih));
+                }
+            }
+        } else if (o.sphere_radius != -1.0f) {              // glsl:759
+            c.kind = RT_KIND_SPHERE;
+            c.hot_index = (int32_t)hs->sph_obj.size();
+            hs->sph_obj.push_back(i);
+            hs->sph.push_back(o.position[0]); hs->sph.push_back(o.position[1]); hs->sph.push_back(o.position[2]);
+            hs->sph.push_back(o.sphere_radius * o.sphere_radius);   // glsl:588 radius * radius
+        } else {
+            c.kind = RT_KIND_SKIP;
+            c.hot_index = -1;
+        }
+    }
+    hs->lights.resize(scene->lights_count > 0 ? scene->lights_count : 0);
+    for (int j = 0; j < scene->lights_count; j++) {
+        const rt_light& L = scene->lights[j];
+        RtLightDev& d = hs->lights[j];
+        memset(&d, 0, sizeof(d));
+        memcpy(d.position, L.position, 12);
+        memcpy(d.ambient, L.ambient, 16);
+        memcpy(d.diffuse, L.diffuse, 16);
+        memcpy(d.specular, L.specular, 16);
+    }
+    return RT_OK;
+}
+
+int validate_scene(const rt_scene* scene) {
+    if (!scene) return fail(RT_ERR_BAD_ARG, "scene is NULL");
+    if (scene->objects_count < 0 || (scene->objects_count > 0 && !scene->objects))
+        return fail(RT_ERR_BAD_ARG, "bad objects / objects_count");
+    if (scene->lights_count < 0 || scene->lights_count > RT_MAX_LIGHTS || (scene->lights_count > 0 && !scene->lights))
+        return fail(RT_ERR_BAD_ARG, "bad lights / lights_count (max %d)", RT_MAX_LIGHTS);
+    if (scene->max_depth < 0 || scene->max_depth > RT_MAX_DEPTH)
+        return fail(RT_ERR_BAD_ARG, "max_depth %d outside 0..%d", scene->max_depth, RT_MAX_DEPTH);
+    return RT_OK;
+}
+
+}  // namespace
+
+// =========================================================================
+// C ABI
+// =========================================================================
+extern "C" {
+
+int rt_abi_version(void) { return RT_ABI_VERSION; }
+const char* rt_last_error_string(void) { return g_err; }
+uint64_t rt_kernel_launch_count(void) { return g_launches.load(); }
+
+void rt_options_default(rt_options* o) {
+    if (!o) return;
+    memset(o, 0, sizeof(*o));
+    o->spp = 1;
+    o->seed = 0x5EED0001u;
+    o->device = -1;
+}
+
+int rt_create(rt_context** out_ctx, int device) {
+    if (!out_ctx) return fail(RT_ERR_BAD_ARG, "out_ctx is NULL");
+    *out_ctx = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(RT_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    if (device < 0) CU(cudaGetDevice(&device));
+    if (device >= ndev) return fail(RT_ERR_BAD_ARG, "device %d out of range (%d devices)", device, ndev);
+    CU(cudaSetDevice(device));
+    rt_context* c = new (std::nothrow) rt_context;
+    if (!c) return fail(RT_ERR_NOMEM, "out of host memory");
+    c->device = device;
+    CU(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    CU(rt_fast::configure(device, &c->max_smem_optin));
+    CU(rt_strict::configure(device, &c->max_smem_optin));
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; i++) CU(cudaEventCreate(&c->ev[i]));
+    CU(c->d_cnt.reserve(1));
+    *out_ctx = c;
+    return RT_OK;
+}
+
+int rt_destroy(rt_context* c) {
+    if (!c) return RT_OK;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    c->d_box_fast.release(); c->d_box_strict.release(); c->d_sph.release();
+    c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
+    c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release();
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return RT_OK;
+}
+
+int rt_synchronize(rt_context* c) {
+    if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_host_alloc(void** ptr, size_t bytes) {
+    if (!ptr || bytes == 0) return fail(RT_ERR_BAD_ARG, "bad rt_host_alloc arguments");
+    CU(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable));
+    return RT_OK;
+}
+int rt_host_free(void* ptr) {
+    if (ptr) CU(cudaFreeHost(ptr));
+    return RT_OK;
+}
+
+int rt_upload_scene(rt_context* c, const rt_scene* scene) {
+    if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
+    int rc = validate_scene(scene);
+    if (rc != RT_OK) return rc;
+    HostScene hs;
+    rc = build_host_scene(scene, &hs);
+    if (rc != RT_OK) return rc;
+    CU(cudaSetDevice(c->device));
+    // The previous frame may still be reading these buffers.
+    CU(cudaStreamSynchronize(c->stream));
+    CU(c->d_box_fast.reserve(hs.box_fast.size() + 4));
+    CU(c->d_box_strict.reserve(hs.box_strict.size() + 4));
+    CU(c->d_sph.reserve(hs.sph.size() + 4));
+    CU(c->d_box_obj.reserve(hs.box_obj.size() + 1));
+    CU(c->d_sph_obj.reserve(hs.sph_obj.size() + 1));
+    CU(c->d_cold.reserve(hs.cold.size() + 1));
+    CU(c->d_lights.reserve(hs.lights.size() + 1));
+    auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
+        if (bytes == 0) return cudaSuccess;
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
+    };
+    CU(up(c->d_box_fast.p, hs.box_fast.data(), hs.box_fast.size() * 4));
+    CU(up(c->d_box_strict.p, hs.box_strict.data(), hs.box_strict.size() * 4));
+    CU(up(c->d_sph.p, hs.sph.data(), hs.sph.size() * 4));
+    CU(up(c->d_box_obj.p, hs.box_obj.data(), hs.box_obj.size() * 4));
+    CU(up(c->d_sph_obj.p, hs.sph_obj.data(), hs.sph_obj.size() * 4));
+    CU(up(c->d_cold.p, hs.cold.data(), hs.cold.size() * sizeof(RtCold)));
+    CU(up(c->d_lights.p, hs.lights.data(), hs.lights.size() * sizeof(RtLightDev)));
+    // pageable sources: the copies above are staged before return, but keep it simple and safe
+    CU(cudaStreamSynchronize(c->stream));
+    c->n_box = (int)hs.box_obj.size();
+    c->n_sph = (int)hs.sph_obj.size();
+    c->n_lights = (int)hs.lights.size();
+    c->max_depth = hs.max_depth;
+    c->have_scene = true;
+    return RT_OK;
+}
+
+int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
+                       void* out_rgba, int width, int height, const rt_options* opts_in) {
+    if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
+    if (!c->have_scene) return fail(RT_ERR_BAD_ARG, "no scene uploaded");
+    if (!cameras || n_frames <= 0) return fail(RT_ERR_BAD_ARG, "bad cameras / n_frames");
+    if (!out_rgba) return fail(RT_ERR_BAD_ARG, "out_rgba is NULL");
+    if (width <= 0 || height <= 0) return fail(RT_ERR_BAD_ARG, "bad image size %dx%d", width, height);
+    rt_options od;
+    rt_options_default(&od);
+    const rt_options& o = opts_in ? *opts_in : od;
+    const int spp = o.spp > 0 ? o.spp : 1;
+    const int y0 = o.y0 > 0 ? o.y0 : 0;
+    const int y1 = (o.y1 > 0 && o.y1 <= height) ? o.y1 : height;
+    if (y0 >= y1) return fail(RT_ERR_BAD_ARG, "empty row band [%d,%d)", y0, y1);
+    if (o.async && !o.out_is_device) return fail(RT_ERR_BAD_ARG, "async requires device output");
+    if (o.device >= 0 && o.device != c->device)
+        return fail(RT_ERR_BAD_ARG, "options.device %d != context device %d", o.device, c->device);
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = o.stream ? (cudaStream_t)o.stream : c->stream;
+
+    // camera prologue (glsl:366-383 hoisted)
+    std::vector<RtCameraDev> cams(n_frames);
+    for (int k = 0; k < n_frames; k++) {
+        const rt_camera& cam = cameras[k];
+        rthm::inverse_proj_view(cam.position, cam.angles, cam.v_fov, cam.aspect, cam.near_plane, cam.far_plane,
+                                cams[k].inv_pv);
+        cams[k].position[0] = cam.position[0]; cams[k].position[1] = cam.position[1];
+        cams[k].position[2] = cam.position[2]; cams[k].position[3] = 1.0f;
+    }
+    if (o.stats) CU(cudaEventRecord(c->ev[2], st));
+    CU(c->d_cams.reserve(n_frames));
+    CU(cudaMemcpyAsync(c->d_cams.p, cams.data(), sizeof(RtCameraDev) * n_frames, cudaMemcpyHostToDevice, st));
+
+    const int band_rows = y1 - y0;
+    const bool band_only = o.out_band_only != 0;
+    const size_t frame_bytes_full = (size_t)width * height * 4;
+    const size_t frame_bytes_band = (size_t)width * band_rows * 4;
+
+    RtParams P;
+    memset(&P, 0, sizeof(P));
+    P.box_hot = reinterpret_cast<const float4*>(o.strict ? c->d_box_strict.p : c->d_box_fast.p);
+    P.sph_hot = reinterpret_cast<const float4*>(c->d_sph.p);
+    P.box_obj = c->d_box_obj.p; P.sph_obj = c->d_sph_obj.p;
+    P.cold = c->d_cold.p; P.lights = c->d_lights.p; P.cams = c->d_cams.p;
+    P.counters = c->d_cnt.p;
+    P.n_box = c->n_box; P.n_sph = c->n_sph; P.n_lights = c->n_lights; P.max_depth = c->max_depth;
+    P.n_frames = n_frames; P.width = width; P.height = height; P.y0 = y0; P.y1 = y1;
+    P.spp = spp; P.seed = o.seed;
+    int n = 1;
+    while ((n + 1) * (n + 1) <= spp) n++;
+    P.spp_n = (n * n == spp) ? n : 0;
+    P.tiles_x = (width + 7) / 8; P.tiles_y = (band_rows + 3) / 4;
+    const size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : RT_BOX_F4_FAST) + P.n_sph) * 16;
+    P.resident = hot_bytes <= (size_t)(c->max_smem_optin / 2 - 2048) ? 1 : 0;
+
+    if (o.out_is_device) {
+        P.out = (uint8_t*)out_rgba;
+        P.frame_stride = band_only ? (long long)frame_bytes_band : (long long)frame_bytes_full;
+        P.out_row0 = band_only ? y0 : 0;
+    } else {
+        // render the band compactly into the context's device buffer, then copy out
+        CU(c->d_out.reserve(frame_bytes_band * n_frames));
+        P.out = c->d_out.p;
+        P.frame_stride = (long long)frame_bytes_band;
+        P.out_row0 = y0;
+    }
+
+    const long long n_tiles = (long long)P.tiles_x * P.tiles_y * n_frames;
+    long long want = (n_tiles + 7) / 8;
+    int grid = 2 * c->sm_count;
+    if (want < grid) grid = (int)(want > 0 ? want : 1);
+
+    const bool count = o.stats != nullptr;
+    if (count) CU(cudaMemsetAsync(c->d_cnt.p, 0, sizeof(RtCounters), st));
+    if (o.stats) CU(cudaEventRecord(c->ev[0], st));
+    CU(o.strict ? rt_strict::launch(P, grid, false, st) : rt_fast::launch(P, grid, false, st));
+    g_launches++;
+    if (o.stats) CU(cudaEventRecord(c->ev[1], st));
+    if (count) {
+        // instrumented twin: same kernel with counters, run after the timed one (results identical)
+        CU(o.strict ? rt_strict::launch(P, grid, true, st) : rt_fast::launch(P, grid, true, st));
+        g_launches++;
+    }
+
+    if (!o.out_is_device) {
+        uint8_t* dst = (uint8_t*)out_rgba;
+        for (int k = 0; k < n_frames; k++) {
+            uint8_t* d = band_only ? dst + (size_t)k * frame_bytes_band
+                                   : dst + (size_t)k * frame_bytes_full + (size_t)y0 * width * 4;
+            CU(cudaMemcpyAsync(d, c->d_out.p + (size_t)k * frame_bytes_band, frame_bytes_band,
+                               cudaMemcpyDeviceToHost, st));
+        }
+    }
+    if (o.stats) CU(cudaEventRecord(c->ev[3], st));
+    if (!o.async) {
+        CU(cudaStreamSynchronize(st));   // glFinish() (main.cpp:238)
+    }
+    if (o.stats) {
+        if (o.async) CU(cudaStreamSynchronize(st));
+        RtCounters hc;
+        CU(cudaMemcpy(&hc, c->d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost));
+        rt_stats* s = o.stats;
+        s->rays = hc.rays; s->nodes = hc.nodes; s->hit_nodes = hc.hit_nodes; s->shadow_rays = hc.shadow_rays;
+        s->box_tests = hc.box_tests; s->sphere_tests = hc.sphere_tests; s->red_pixels = hc.red_pixels;
+        CU(cudaEventElapsedTime(&s->kernel_ms, c->ev[0], c->ev[1]));
+        CU(cudaEventElapsedTime(&s->total_ms, c->ev[2], c->ev[3]));
+    }
+    return RT_OK;
+}
+
+int rt_render_batch(rt_context* c, const rt_scene* scene, const rt_camera* cameras, int n_frames,
+                    void* out_rgba, int width, int height, const rt_options* opts) {
+    int rc = rt_upload_scene(c, scene);
+    if (rc != RT_OK) return rc;
+    return rt_render_uploaded(c, cameras, n_frames, out_rgba, width, height, opts);
+}
+
+int rt_render_ex(rt_context* c, const rt_scene* scene, const rt_camera* camera, void* out_rgba,
+                 int width, int height, const rt_options* opts) {
+    if (!camera) return fail(RT_ERR_BAD_ARG, "camera_uniforms is NULL");
+    return rt_render_batch(c, scene, camera, 1, out_rgba, width, height, opts);
+}
+
+int rt_render(const rt_scene* scene, const rt_camera* camera, uint8_t* out_rgba, int width, int height) {
+    static std::mutex mu;
+    static rt_context* ctxs[64] = {nullptr};
+    int dev = 0;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(RT_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(RT_ERR_BAD_ARG, "device ordinal %d unsupported", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ctxs[dev]) {
+        int rc = rt_create(&ctxs[dev], dev);
+        if (rc != RT_OK) return rc;
+    }
+    return rt_render_ex(ctxs[dev], scene, camera, out_rgba, width, height, nullptr);
+}
+
+int rt_ipc_export(void* device_ptr, uint8_t handle64[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (!device_ptr || !handle64) return fail(RT_ERR_BAD_ARG, "bad rt_ipc_export arguments");
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, device_ptr));
+    memcpy(handle64, &h, 64);
+    return RT_OK;
+}
+int rt_ipc_import(const uint8_t handle64[64], void** device_ptr) {
+    if (!device_ptr || !handle64) return fail(RT_ERR_BAD_ARG, "bad rt_ipc_import arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    CU(cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RT_OK;
+}
+int rt_ipc_close(void* device_ptr) {
+    if (device_ptr) CU(cudaIpcCloseMemHandle(device_ptr));
+    return RT_OK;
+}
+
+}  // extern "C"
