@@ -1,0 +1,249 @@
+"""GPU parity tests: the CUDA kernel, called through the C ABI, against the CPU
+oracle on the same scene / camera / resolution.
+
+Tolerance (north_star): <= 1 LSB per RGBA8 channel on >= 99.9 % of pixels; the
+pixels beyond 1 LSB are counted and must sit on silhouette / shadow edges of the
+oracle image (an FP hit decision flipped).  Multi-band, batch and device-output
+paths must be BYTE-identical to the single-call host path.
+"""
+import ctypes as C
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import openglraytracer_b200 as rt
+import oracle_binding as ob
+from parity import TOL_LSB, assert_parity, compare, edge_mask
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def tracer():
+    r = rt.Raytracer(0)
+    yield r
+    r.close()
+
+
+def _check(img, ref, what, need_edges=True):
+    rep = assert_parity(img, ref, what)
+    assert int(img[..., 3].max()) == 0, "alpha must be 0 (glsl:404)"
+    if need_edges and rep["over_1"] and ref.ndim == 3:
+        d = np.abs(img.astype(np.int16) - ref.astype(np.int16)).max(axis=2)
+        bad = d > TOL_LSB
+        on_edge = bad & edge_mask(ref, radius=2)
+        # larger diffs are confined to silhouette / shadow / refraction edges
+        assert on_edge.sum() >= 0.8 * bad.sum(), "%s: %d of %d large diffs off-edge" % (
+            what, int(bad.sum() - on_edge.sum()), int(bad.sum()))
+    return rep
+
+
+@pytest.mark.parametrize("strict", [True, False])
+@pytest.mark.parametrize("time,depth,w,h", [(0.0, 0, 1280, 720), (0.0, 2, 640, 360), (2.5, 4, 640, 360),
+                                            (3.7, 4, 320, 180), (7.25, 6, 160, 90), (11.0, 8, 96, 54)])
+def test_builtin_scene_vs_oracle(tracer, strict, time, depth, w, h):
+    sc, cam = rt.builtin_scene(time, depth), rt.builtin_camera(time)
+    ref, ost = ob.render(sc, cam, w, h, want_stats=True)
+    img, st = tracer.render(sc, cam, w, h, strict=strict, want_stats=True)
+    rep = _check(img, ref, "builtin t=%g d=%d %s" % (time, depth, "strict" if strict else "fast"))
+    if strict:
+        assert rep["frac_exact"] >= 0.9995       # op-for-op arithmetic: only powf / weight-order ulps remain
+    # the ray accounting is the reference's: one ray per get_closest_collision call
+    assert abs(st["rays"] - ost["rays"]) <= 1e-4 * ost["rays"] + 8
+    assert st["sphere_tests"] <= ost["sphere_tests"] and st["box_tests"] <= ost["box_tests"]  # any-hit exits early
+
+
+def test_golden_fixtures_on_gpu(tracer):
+    with open(os.path.join(HERE, "golden", "golden.json")) as f:
+        gold = json.load(f)
+    npz = np.load(os.path.join(HERE, "golden", "golden_images.npz"))
+    for name in npz.files:
+        t, d, w, h = name.split("_")
+        t, d, w, h = float(t[1:]), int(d[1:]), int(w[1:]), int(h[1:])
+        for strict in (True, False):
+            img = tracer.render(rt.builtin_scene(t, d), rt.builtin_camera(t), w, h, strict=strict)
+            _check(img, npz[name], "golden %s strict=%s" % (name, strict))
+    # strict kernel reproduces the shipped-depth golden frame hash bit for bit
+    case = [c for c in gold["cases"] if c["depth"] == 0 and c["width"] == 1280][0]
+    img = tracer.render(rt.builtin_scene(0.0, 0), rt.builtin_camera(0.0), 1280, 720, strict=True)
+    assert hashlib.sha256(img.tobytes()).hexdigest() == case["sha256"]
+
+
+def test_drop_in_rt_render_call():
+    sc, cam = rt.builtin_scene(1.0), rt.builtin_camera(1.0)
+    img = rt.render(sc, cam, 320, 180)          # rt_render(scene, camera_uniforms, out_rgba, w, h)
+    _check(img, ob.render(sc, cam, 320, 180), "rt_render")
+
+
+@pytest.mark.parametrize("w,h", [(1, 1), (7, 5), (33, 17), (130, 3), (8, 4), (9, 1)])
+def test_ragged_sizes(tracer, w, h):
+    sc, cam = rt.builtin_scene(0.3, 2), rt.builtin_camera(0.3)
+    for strict in (True, False):
+        img = tracer.render(sc, cam, w, h, strict=strict)
+        rep = compare(img, ob.render(sc, cam, w, h))
+        assert rep["over_1"] <= max(1, int(0.02 * w * h)), rep
+
+
+def test_time_sweep_strict(tracer):
+    for k in range(12):
+        t = 0.37 * k
+        sc, cam = rt.builtin_scene(t, 1), rt.builtin_camera(t)
+        _check(tracer.render(sc, cam, 160, 90, strict=True), ob.render(sc, cam, 160, 90), "sweep t=%g" % t)
+
+
+def test_jittered_spp(tracer):
+    sc, cam = rt.builtin_scene(0.0, 2), rt.builtin_camera(0.0)
+    for spp in (4, 16, 5):
+        ref = ob.render(sc, cam, 160, 90, spp=spp)
+        for strict in (True, False):
+            _check(tracer.render(sc, cam, 160, 90, spp=spp, strict=strict), ref, "spp=%d" % spp, need_edges=False)
+    a = tracer.render(sc, cam, 160, 90, spp=4, seed=1)
+    b = tracer.render(sc, cam, 160, 90, spp=4, seed=2)
+    assert not np.array_equal(a, b)
+
+
+def test_row_bands_are_byte_identical_to_full_frame(tracer):
+    sc, cam = rt.builtin_scene(0.9, 3), rt.builtin_camera(0.9)
+    w, h = 256, 147
+    full = tracer.render(sc, cam, w, h)
+    for world in (2, 3, 8):
+        canvas = np.zeros_like(full)
+        for r in range(world):
+            y0, y1 = (r * h) // world, ((r + 1) * h) // world
+            band = tracer.render(sc, cam, w, h, y0=y0, y1=y1, band_only=True)
+            assert band.shape == (y1 - y0, w, 4)
+            canvas[y0:y1] = band
+        assert np.array_equal(canvas, full)
+    # band written in place into a full-size caller buffer
+    out = np.full_like(full, 9)
+    tracer.render(sc, cam, w, h, y0=40, y1=100, out=out)
+    assert np.array_equal(out[40:100], full[40:100]) and (out[:40] == 9).all() and (out[100:] == 9).all()
+
+
+def test_batch_equals_single_frames(tracer):
+    sc = rt.builtin_scene(0.0, 2)
+    cams = rt.turntable_cameras(6)
+    batch = tracer.render(sc, cams, 128, 72)
+    assert batch.shape == (6, 72, 128, 4)
+    for k in range(6):
+        assert np.array_equal(batch[k], tracer.render(sc, cams[k], 128, 72))
+    _check(batch[3], ob.render(sc, cams[3], 128, 72), "batch frame 3")
+
+
+def test_device_output_and_pinned_host(tracer):
+    import torch
+    sc, cam = rt.builtin_scene(0.0, 1), rt.builtin_camera(0.0)
+    w, h = 200, 120
+    ref = tracer.render(sc, cam, w, h)
+    dev = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
+    torch.cuda.synchronize()
+    tracer.render(sc, cam, w, h, out_device_ptr=dev.data_ptr())
+    assert np.array_equal(dev.cpu().numpy(), ref)
+    pin = rt.PinnedImage((h, w, 4))
+    tracer.render(sc, cam, w, h, out=pin.array)
+    assert np.array_equal(pin.array, ref)
+    pin.free()
+
+
+@pytest.mark.parametrize("n,depth", [(64, 2), (1024, 1), (4096, 1)])
+def test_scaled_scene_small_frames(tracer, n, depth):
+    sc, cam = rt.scaled_scene(n, max_depth=depth), rt.builtin_camera(0.0)
+    ref = ob.render(sc, cam, 256, 144)
+    _check(tracer.render(sc, cam, 256, 144, strict=True), ref, "scaled n=%d strict" % n)
+    _check(tracer.render(sc, cam, 256, 144, strict=False), ref, "scaled n=%d fast" % n)
+
+
+@pytest.mark.parametrize("n", [16384, 65536])
+def test_scaled_scene_streaming_pixel_subset(tracer, n):
+    # full-resolution frame, oracle on a seeded 4096-pixel subset
+    sc, cam = rt.scaled_scene(n, max_depth=0), rt.builtin_camera(0.0)
+    w, h = 1920, 1080
+    rng = np.random.default_rng(0x5CE7E001)
+    npix = 4096 if n <= 16384 else 1024
+    pix = np.stack([rng.integers(0, w, npix), rng.integers(0, h, npix)], axis=1).astype(np.int32)
+    ref = ob.render(sc, cam, w, h, pixels=pix)
+    # render only the rows we need in chunks to keep the GPU time small: full frame is the product path
+    img = tracer.render(sc, cam, w, h)
+    got = img[pix[:, 1], pix[:, 0]]
+    assert_parity(got, ref, "scaled n=%d subset" % n)
+
+
+def test_edge_case_scenes(tracer):
+    cam = rt.builtin_camera(0.0)
+    # empty scene: every ray misses -> black, alpha 0 (semantics item 7)
+    empty = rt.SceneData((rt.Object * 1)(), (rt.Light * 1)(), 0)
+    empty.scene.objects_count = 0
+    empty.scene.lights_count = 0
+    img = tracer.render(empty, cam, 40, 30)
+    assert img.max() == 0
+    # null objects are skipped; zero-thickness box never hits; no lights -> emissive/ambient only
+    base = rt.builtin_scene(0.0, 2)
+    objs = (rt.Object * 8)()
+    for i in range(5):
+        objs[i] = base.objects[i]
+    objs[5].sphere_radius = -1.0                                   # null box + null sphere
+    objs[6].box_mins[:] = [-1, -1, 0]
+    objs[6].box_maxs[:] = [1, 1, 0]                                 # flat box
+    objs[6].sphere_radius = -1.0
+    objs[6].position[:] = [4, 2, 0]
+    objs[7].sphere_radius = 0.5
+    objs[7].position[:] = [5, 3, 1]
+    objs[7].material = base.objects[4].material
+    sc = rt.SceneData(objs, base.lights, 2)
+    ref = ob.render(sc, cam, 160, 90)
+    for strict in (True, False):
+        _check(tracer.render(sc, cam, 160, 90, strict=strict), ref, "mixed scene strict=%s" % strict)
+    nolight = rt.SceneData(objs, (rt.Light * 1)(), 1)
+    nolight.scene.lights_count = 0
+    assert np.array_equal(tracer.render(nolight, cam, 64, 36, strict=True), ob.render(nolight, cam, 64, 36))
+
+
+def test_runaway_guard_red_pixels_match(tracer):
+    sc, cam = rt.builtin_scene(3.7, 15), rt.builtin_camera(3.7)
+    ref, ost = ob.render(sc, cam, 64, 36, want_stats=True)
+    img, st = tracer.render(sc, cam, 64, 36, strict=True, want_stats=True)
+    assert ost["red_pixels"] > 0
+    red_ref = (ref[..., 0] == 255) & (ref[..., 1] == 0) & (ref[..., 2] == 0)
+    red_gpu = (img[..., 0] == 255) & (img[..., 1] == 0) & (img[..., 2] == 0)
+    assert (red_ref != red_gpu).sum() <= 2 and abs(int(st["red_pixels"]) - int(ost["red_pixels"])) <= 2
+
+
+def test_bad_arguments_are_rejected(tracer):
+    sc, cam = rt.builtin_scene(), rt.builtin_camera()
+    with pytest.raises(rt.RtError):
+        tracer.render(sc.with_depth(rt.RT_MAX_DEPTH + 1), cam, 16, 9)
+    sc.with_depth(0)
+    with pytest.raises(rt.RtError):
+        tracer.render(sc, cam, 0, 9)
+    with pytest.raises(rt.RtError):
+        tracer.render(sc, cam, 16, 9, y0=5, y1=5)
+
+
+def test_full_size_properties_1080p_and_4k(tracer):
+    """At BASELINE sizes the oracle is too slow for a full compare in the GPU
+    suite; use size-independent properties: determinism, band union == frame,
+    alpha == 0, oracle agreement on a seeded pixel subset."""
+    sc, cam = rt.builtin_scene(0.0, 4), rt.builtin_camera(0.0)
+    for (w, h, spp) in [(1920, 1080, 1), (3840, 2160, 4)]:
+        a = tracer.render(sc, cam, w, h, spp=spp)
+        b = tracer.render(sc, cam, w, h, spp=spp)
+        assert np.array_equal(a, b) and a[..., 3].max() == 0
+        canvas = np.empty_like(a)
+        for r in range(8):
+            y0, y1 = (r * h) // 8, ((r + 1) * h) // 8
+            canvas[y0:y1] = tracer.render(sc, cam, w, h, spp=spp, y0=y0, y1=y1, band_only=True)
+        assert np.array_equal(canvas, a)
+        rng = np.random.default_rng(w)
+        pix = np.stack([rng.integers(0, w, 4096), rng.integers(0, h, 4096)], axis=1).astype(np.int32)
+        ref = ob.render(sc, cam, w, h, spp=spp, pixels=pix)
+        assert_parity(a[pix[:, 1], pix[:, 0]], ref, "%dx%d subset" % (w, h))
+
+
+def test_kernels_actually_launch(tracer):
+    before = rt.kernel_launch_count()
+    tracer.render(rt.builtin_scene(), rt.builtin_camera(), 64, 36)
+    assert rt.kernel_launch_count() == before + 1

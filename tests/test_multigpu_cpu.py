@@ -1,0 +1,64 @@
+"""world_size-2 gloo test of the N>1 host logic on CPU: contiguous row bands,
+padded gather on rank 0, assembled frame byte-identical to the single-rank frame.
+The band pixels come from the oracle here (no GPU in this container); on the GPU
+box tests/test_gpu_parity.py runs the same assembly with the CUDA kernel."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from openglraytracer_b200.multigpu import frame_block, gather_bands, row_band
+
+
+def test_row_bands_partition_rows_exactly():
+    for h in (1, 7, 270, 720, 1080, 2160, 2161):
+        for g in (1, 2, 3, 4, 8):
+            bands = [row_band(r, g, h) for r in range(g)]
+            assert bands[0][0] == 0 and bands[-1][1] == h
+            assert all(bands[i][1] == bands[i + 1][0] for i in range(g - 1))
+            rows = [b - a for a, b in bands]
+            assert max(rows) - min(rows) <= 1
+    assert row_band(3, 8, 2160) == (810, 1080)       # 270-row bands at 4K / 8 GPUs
+    assert [frame_block(r, 8, 256) for r in (0, 7)] == [(0, 32), (224, 256)]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, w, h, out_path):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import oracle_binding as ob
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sc, cam = ob.builtin_scene(0.7, 2), ob.builtin_camera(0.7)
+    y0, y1 = row_band(rank, world, h)
+    full_canvas = ob.render(sc, cam, w, h, y0=y0, y1=y1, threads=2)     # absolute pixel coords (glsl:377-378)
+    band = torch.from_numpy(np.ascontiguousarray(full_canvas[y0:y1]))
+    frame = gather_bands(band, h, w)
+    if rank == 0:
+        np.save(out_path, frame.numpy())
+    else:
+        assert frame is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,h", [(2, 45), (3, 46)])
+def test_band_gather_is_byte_identical_to_single_rank(tmp_path, world, h):
+    import oracle_binding as ob
+    w = 80
+    out = str(tmp_path / "frame.npy")
+    mp.spawn(_worker, args=(world, _free_port(), w, h, out), nprocs=world, join=True)
+    ref = ob.render(ob.builtin_scene(0.7, 2), ob.builtin_camera(0.7), w, h)
+    assert np.array_equal(np.load(out), ref)
