@@ -221,7 +221,9 @@ def run_gpu(args, wl_name, wl):
     scene = make_scene(rt, kind, n_obj, depth)
     cam = rt.builtin_camera(0.0)
     tracer = rt.Raytracer(local)
-    stream = torch.cuda.current_stream(dev)
+    # a real (non-NULL) stream: the C ABI treats a NULL stream as "the context's own stream"
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
     frame_dev = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
 

@@ -61,14 +61,22 @@ class BandRenderer:
         self.rank, self.world = rank, world
         self.y0, self.y1 = row_band(rank, world, height)
         self.band = torch.empty((self.y1 - self.y0, width, 4), dtype=torch.uint8, device=device)
+        # A real stream handle: the C ABI reads a NULL stream as "the context's own stream",
+        # and torch's legacy default stream IS the NULL handle.
+        self.stream = torch.cuda.Stream(device)
 
     def render(self, scene, camera, **kw):
-        """Launch the band render on torch's current stream (asynchronous)."""
-        stream = torch.cuda.current_stream(self.band.device).cuda_stream
+        """Launch the band render on this renderer's stream (asynchronous), ordered after
+        whatever the caller's current stream has queued."""
+        self.stream.wait_stream(torch.cuda.current_stream(self.band.device))
+        stream = self.stream.cuda_stream
         self.rt.render(scene, camera, self.width, self.height, y0=self.y0, y1=self.y1, band_only=True,
                        out_device_ptr=self.band.data_ptr(), async_=True, stream=stream, **kw)
         return self.band
 
     def render_and_gather(self, scene, camera, group=None, **kw):
         band = self.render(scene, camera, **kw)
-        return gather_bands(band, self.height, self.width, group=group)
+        with torch.cuda.stream(self.stream):
+            frame = gather_bands(band, self.height, self.width, group=group)
+        torch.cuda.current_stream(self.band.device).wait_stream(self.stream)
+        return frame

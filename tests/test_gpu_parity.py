@@ -37,8 +37,10 @@ def _check(img, ref, what, need_edges=True):
         bad = d > TOL_LSB
         on_edge = bad & edge_mask(ref, radius=2)
         # larger diffs are confined to silhouette / shadow / refraction edges
-        assert on_edge.sum() >= 0.8 * bad.sum(), "%s: %d of %d large diffs off-edge" % (
-            what, int(bad.sum() - on_edge.sum()), int(bad.sum()))
+        # (a flip deep inside a refraction chain lands anywhere inside the glass: allow a handful)
+        off_edge = int(bad.sum() - on_edge.sum())
+        assert off_edge <= max(3, int(2e-5 * bad.size)), "%s: %d of %d large diffs off-edge" % (
+            what, off_edge, int(bad.sum()))
     return rep
 
 
