@@ -83,60 +83,67 @@ struct Slabs { float t1x, t1y, t1z, t2x, t2y, t2z; };
 
 #if RT_STRICT
 // hot record: r0,r1,r2 = world->local rows, r3 = (mins.xyz, maxs.x), r4 = (maxs.y, maxs.z, -, -)
-__device__ __forceinline__ void box_slabs(const float4* __restrict__ rec, V3 o, V3 d,
+// (world_to_local * vec4(start,1)).xyz, glsl:655
+__device__ __forceinline__ V3 box_origin(const float4* __restrict__ rec, V3 o) {
+    const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
+    V3 s;
+    s.x = ((r0.x * o.x + r0.y * o.y) + r0.z * o.z) + r0.w * 1.0f;
+    s.y = ((r1.x * o.x + r1.y * o.y) + r1.z * o.z) + r1.w * 1.0f;
+    s.z = ((r2.x * o.x + r2.y * o.y) + r2.z * o.z) + r2.w * 1.0f;
+    return s;
+}
+__device__ __forceinline__ void box_slabs(const float4* __restrict__ rec, V3 so, V3 d,
                                           float& tn, float& tf, Slabs& s, V3& ld) {
     const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2], r3 = rec[3], r4 = rec[4];
-    // (world_to_local * vec4(start,1)).xyz and (world_to_local * vec4(dir,0)).xyz, glsl:655-656
-    float sx = ((r0.x * o.x + r0.y * o.y) + r0.z * o.z) + r0.w * 1.0f;
-    float sy = ((r1.x * o.x + r1.y * o.y) + r1.z * o.z) + r1.w * 1.0f;
-    float sz = ((r2.x * o.x + r2.y * o.y) + r2.z * o.z) + r2.w * 1.0f;
+    // (world_to_local * vec4(dir,0)).xyz, glsl:656
     ld.x = ((r0.x * d.x + r0.y * d.y) + r0.z * d.z) + r0.w * 0.0f;
     ld.y = ((r1.x * d.x + r1.y * d.y) + r1.z * d.z) + r1.w * 0.0f;
     ld.z = ((r2.x * d.x + r2.y * d.y) + r2.z * d.z) + r2.w * 0.0f;
-    float tminx = (r3.x - sx) / ld.x, tmaxx = (r3.w - sx) / ld.x;   // glsl:661-662
-    float tminy = (r3.y - sy) / ld.y, tmaxy = (r4.x - sy) / ld.y;
-    float tminz = (r3.z - sz) / ld.z, tmaxz = (r4.y - sz) / ld.z;
-    s.t1x = fminf(tminx, tmaxx); s.t2x = fmaxf(tminx, tmaxx);       // glsl:663-664
+    float tminx = (r3.x - so.x) / ld.x, tmaxx = (r3.w - so.x) / ld.x;   // glsl:661-662
+    float tminy = (r3.y - so.y) / ld.y, tmaxy = (r4.x - so.y) / ld.y;
+    float tminz = (r3.z - so.z) / ld.z, tmaxz = (r4.y - so.z) / ld.z;
+    s.t1x = fminf(tminx, tmaxx); s.t2x = fmaxf(tminx, tmaxx);           // glsl:663-664
     s.t1y = fminf(tminy, tmaxy); s.t2y = fmaxf(tminy, tmaxy);
     s.t1z = fminf(tminz, tmaxz); s.t2z = fmaxf(tminz, tmaxz);
-    tn = fmaxf(fmaxf(s.t1x, s.t1y), s.t1z);                          // glsl:665
-    tf = fminf(fminf(s.t2x, s.t2y), s.t2z);                          // glsl:666
+    tn = fmaxf(fmaxf(s.t1x, s.t1y), s.t1z);                              // glsl:665
+    tf = fminf(fminf(s.t2x, s.t2y), s.t2z);                              // glsl:666
 }
-// glsl:680, 690-696, 753: returns t > 0 on a hit, -1 on a miss
-__device__ __forceinline__ float box_t(float tn, float tf) {
-    if (tn >= tf || tf <= 0.0f) return -1.0f;
-    return (tn < 0.0f) ? tf : tn;
-}
+// glsl:680: "the ray didn't intersect the box"
+__device__ __forceinline__ bool box_reject(float tn, float tf) { return tn >= tf || tf <= 0.0f; }
 #else
-// hot record: rows of diag(1/h) * (world_to_local - centre): local'' = r * (p,1)
-__device__ __forceinline__ void box_slabs(const float4* __restrict__ rec, V3 o, V3 d,
+// hot record: rows of diag(1/h) * (world_to_local - centre): local'' = r * (p, 1), the box is [-1,1]^3
+__device__ __forceinline__ V3 box_origin(const float4* __restrict__ rec, V3 o) {
+    const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
+    V3 s;
+    s.x = __fmaf_rn(r0.x, o.x, __fmaf_rn(r0.y, o.y, __fmaf_rn(r0.z, o.z, r0.w)));
+    s.y = __fmaf_rn(r1.x, o.x, __fmaf_rn(r1.y, o.y, __fmaf_rn(r1.z, o.z, r1.w)));
+    s.z = __fmaf_rn(r2.x, o.x, __fmaf_rn(r2.y, o.y, __fmaf_rn(r2.z, o.z, r2.w)));
+    return s;
+}
+// t = (+-1 - s)/d per axis as  n = -s*inv,  t1 = n - |inv|,  t2 = n + |inv|  (1 MUFU.RCP + 3 FP32 ops).
+// The 1e-30 seed of the direction FMA chain keeps d'' away from an exact 0 (whose reciprocal would
+// give inf - inf = NaN and lose the "parallel and outside the slab -> miss" decision, glsl:661-666)
+// at no instruction cost; it is 2^-76 relative to any direction component that matters.
+__device__ __forceinline__ void box_slabs(const float4* __restrict__ rec, V3 so, V3 d,
                                           float& tn, float& tf, Slabs& s, V3& ld) {
     const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
-    float sx = __fmaf_rn(r0.x, o.x, __fmaf_rn(r0.y, o.y, __fmaf_rn(r0.z, o.z, r0.w)));
-    float sy = __fmaf_rn(r1.x, o.x, __fmaf_rn(r1.y, o.y, __fmaf_rn(r1.z, o.z, r1.w)));
-    float sz = __fmaf_rn(r2.x, o.x, __fmaf_rn(r2.y, o.y, __fmaf_rn(r2.z, o.z, r2.w)));
-    ld.x = __fmaf_rn(r0.x, d.x, __fmaf_rn(r0.y, d.y, __fmul_rn(r0.z, d.z)));
-    ld.y = __fmaf_rn(r1.x, d.x, __fmaf_rn(r1.y, d.y, __fmul_rn(r1.z, d.z)));
-    ld.z = __fmaf_rn(r2.x, d.x, __fmaf_rn(r2.y, d.y, __fmul_rn(r2.z, d.z)));
-    // |d| clamped away from 0 keeps every value finite (no inf-inf / 0*inf NaN);
-    // a parallel ray outside the slab still misses, inside it the slab is ignored.
-    float ax = rcp_approx(fmaxf(fabsf(ld.x), 1e-30f));
-    float ay = rcp_approx(fmaxf(fabsf(ld.y), 1e-30f));
-    float az = rcp_approx(fmaxf(fabsf(ld.z), 1e-30f));
-    float ix = copysignf(ax, ld.x), iy = copysignf(ay, ld.y), iz = copysignf(az, ld.z);
-    s.t1x = __fmaf_rn(-sx, ix, -ax); s.t2x = __fmaf_rn(-sx, ix, ax);
-    s.t1y = __fmaf_rn(-sy, iy, -ay); s.t2y = __fmaf_rn(-sy, iy, ay);
-    s.t1z = __fmaf_rn(-sz, iz, -az); s.t2z = __fmaf_rn(-sz, iz, az);
+    ld.x = __fmaf_rn(r0.x, d.x, __fmaf_rn(r0.y, d.y, __fmaf_rn(r0.z, d.z, 1e-30f)));
+    ld.y = __fmaf_rn(r1.x, d.x, __fmaf_rn(r1.y, d.y, __fmaf_rn(r1.z, d.z, 1e-30f)));
+    ld.z = __fmaf_rn(r2.x, d.x, __fmaf_rn(r2.y, d.y, __fmaf_rn(r2.z, d.z, 1e-30f)));
+    const float ix = rcp_approx(ld.x), iy = rcp_approx(ld.y), iz = rcp_approx(ld.z);
+    const float nx = __fmul_rn(-so.x, ix), ny = __fmul_rn(-so.y, iy), nz = __fmul_rn(-so.z, iz);
+    s.t1x = __fadd_rn(nx, -fabsf(ix)); s.t2x = __fadd_rn(nx, fabsf(ix));
+    s.t1y = __fadd_rn(ny, -fabsf(iy)); s.t2y = __fadd_rn(ny, fabsf(iy));
+    s.t1z = __fadd_rn(nz, -fabsf(iz)); s.t2z = __fadd_rn(nz, fabsf(iz));
     tn = fmaxf(fmaxf(s.t1x, s.t1y), s.t1z);
     tf = fminf(fminf(s.t2x, s.t2y), s.t2z);
 }
-// Same decisions as glsl:680, 690-696, 753 for finite inputs: hit iff
-// t_near < t_far and the chosen t (t_far when the origin is inside) is > 0.
-__device__ __forceinline__ float box_t(float tn, float tf) {
-    float t = (tn < 0.0f) ? tf : tn;
-    return (tn < tf) ? t : -1.0f;
-}
+// All values are finite here, so "t_near >= t_far" (glsl:680) is exactly !(tn < tf); the t_far <= 0
+// half of the reject is covered by the caller's t > 0 (glsl:753) because t = t_far when t_near < 0.
+__device__ __forceinline__ bool box_reject(float tn, float tf) { return !(tn < tf); }
 #endif
+// glsl:690-696: the ray started inside the box -> the hit is the exit point
+__device__ __forceinline__ float box_pick(float tn, float tf) { return (tn < 0.0f) ? tf : tn; }
 
 // -------------------------------------------------------------------------
 // Ray / sphere test (glsl:585-625).  c = (centre, r*r).  Returns t (or <= 0 / NaN
@@ -188,9 +195,14 @@ __device__ __forceinline__ RayQ ray_q(V3 d) {
 // best[r] comes in as t_max (10000 for closest-hit rays, 1 for shadow rays,
 // 0 for an inactive slot) and goes out as the smallest accepted t; bidx[r] is
 // the hot-list position of the winner (boxes 0..n_box-1, spheres n_box..) or -1.
-// The loop trip count is warp-uniform.  ANYHIT adds a warp-vote early exit.
+// The loop trip count is warp-uniform.
+//   SHARED : all R rays start at o[0] (the shadow rays of one hit point,
+//            glsl:808) -> the origin is moved into the box frame once per box.
+//   ANYHIT : shadow semantics (glsl:816: in shadow iff closest t < 1, i.e. iff
+//            ANY object is hit at 0 < t < 1): no index, warp-vote early exit.
+// Most tests miss, so the accept logic sits behind one warp vote per box.
 // -------------------------------------------------------------------------
-template <int R, bool SMEM, bool ANYHIT, bool COUNT>
+template <int R, bool SMEM, bool ANYHIT, bool SHARED, bool COUNT>
 __device__ __forceinline__ void trace(const RtParams& P, const float4* __restrict__ box_hot,
                                       const float4* __restrict__ sph_hot,
                                       const V3 (&o)[R], const V3 (&d)[R], float (&best)[R], int (&bidx)[R],
@@ -202,13 +214,24 @@ __device__ __forceinline__ void trace(const RtParams& P, const float4* __restric
         float4 rec[RT_BOX_F4];
 #pragma unroll
         for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = SMEM ? box_hot[i * RT_BOX_F4 + k] : __ldg(box_hot + i * RT_BOX_F4 + k);
+        float tn[R], tf[R];
+        bool cand = false;
+        V3 so;
+        if (SHARED) so = box_origin(rec, o[0]);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             if (COUNT) n_box_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
-            float tn, tf; Slabs s; V3 ld;
-            box_slabs(rec, o[r], d[r], tn, tf, s, ld);
-            float t = box_t(tn, tf);
-            if (t > 0.0f && t < best[r]) { best[r] = t; bidx[r] = i; }
+            if (!SHARED) so = box_origin(rec, o[r]);
+            Slabs s; V3 ld;
+            box_slabs(rec, so, d[r], tn[r], tf[r], s, ld);
+            cand = cand || !box_reject(tn[r], tf[r]);
+        }
+        if (__any_sync(kFull, cand)) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float t = box_pick(tn[r], tf[r]);
+                if (!box_reject(tn[r], tf[r]) && t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = i; }
+            }
         }
         if (ANYHIT && (i & 15) == 15) {
             bool done = true;
@@ -229,8 +252,8 @@ __device__ __forceinline__ void trace(const RtParams& P, const float4* __restric
         for (int r = 0; r < R; ++r) {
             if (COUNT) n_sph_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
             bool inside;
-            float t = sphere_t(c, o[r], d[r], q[r], inside);
-            if (t > 0.0f && t < best[r]) { best[r] = t; bidx[r] = n_box + j; }
+            float t = sphere_t(c, o[SHARED ? 0 : r], d[r], q[r], inside);
+            if (t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = n_box + j; }
             else if (!ANYHIT && t == best[r] && bidx[r] >= 0 && bidx[r] < n_box) {
                 // exact tie with a box: the lower ORIGINAL index wins (glsl:773 strict '<' in index order)
                 if (__ldg(P.sph_obj + j) < __ldg(P.box_obj + bidx[r])) bidx[r] = n_box + j;
@@ -279,7 +302,7 @@ __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const float4* __re
 #pragma unroll
     for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = SMEM ? box_hot[bidx * RT_BOX_F4 + k] : __ldg(box_hot + bidx * RT_BOX_F4 + k);
     float tn, tf; Slabs s; V3 ld;
-    box_slabs(rec, o, d, tn, tf, s, ld);
+    box_slabs(rec, box_origin(rec, o), d, tn, tf, s, ld);
     h.inside = tn < 0.0f;                                           // glsl:690-696
     const float by = h.inside ? s.t2y : s.t1y, bz = h.inside ? s.t2z : s.t1z;
     int face = 0;                                                   // glsl:699-704
@@ -394,7 +417,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
             best[0] = 0.0f;
         }
         // PHASE 0 (glsl:956-967)
-        trace<1, SMEM, false, COUNT>(P, box_hot, sph_hot, o, d, best, bidx, cnt.box_tests, cnt.sphere_tests);
+        trace<1, SMEM, false, false, COUNT>(P, box_hot, sph_hot, o, d, best, bidx, cnt.box_tests, cnt.sphere_tests);
         const bool hit = act && bidx[0] >= 0;
         if (COUNT && act) { cnt.rays++; cnt.nodes++; cnt.hit_nodes += hit; }
         if (act) iters += hit ? 6 : 1;
@@ -427,7 +450,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
                         sb[r] = 0.0f;
                     }
                 }
-                trace<kShadowBatch, SMEM, true, COUNT>(P, box_hot, sph_hot, so, sd, sb, si, cnt.box_tests, cnt.sphere_tests);
+                trace<kShadowBatch, SMEM, true, true, COUNT>(P, box_hot, sph_hot, so, sd, sb, si, cnt.box_tests, cnt.sphere_tests);
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     const int l = l0 + r;
@@ -436,7 +459,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
                         const RtLightDev* __restrict__ L = P.lights + l;
 #pragma unroll
                         for (int k = 0; k < 4; ++k) amb[k] += L->ambient[k] * mat->ambient[k];     // glsl:801
-                        const bool in_shadow = si[r] >= 0;
+                        const bool in_shadow = sb[r] < 1.0f;
                         if (!in_shadow) {
                             const V3 light_dir = normalize3(sd[r]);                                  // glsl:804
                             const V3 light_ref = normalize3(reflect3(-light_dir, h.n));              // glsl:825
