@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB", os.path.join(_HERE, "librt_b200.so"))   # override: kernel experiments only
 
 RT_OK = 0
 RT_ERR_BAD_ARG = -1

@@ -77,6 +77,7 @@ struct RtParams {
     const RtCameraDev* cams;
     uint8_t* out;               /* frame k at out + k*frame_stride */
     RtCounters* counters;       /* used by the instrumented twin only */
+    unsigned long long* tile_counter;  /* dynamic tile scheduler, zeroed before each launch */
     long long frame_stride;     /* bytes */
     int32_t n_box, n_sph, n_lights, max_depth;
     int32_t n_frames, width, height, y0, y1;

@@ -33,12 +33,14 @@ static_assert(sizeof(rt_camera) == 10 * 4, "rt_camera must be 10 words (glsl:36-
 static_assert(sizeof(RtCold) == 64 * 4, "cold record must be 256 bytes");
 
 namespace rt_fast {
-cudaError_t launch(const RtParams& P, int grid, bool count, cudaStream_t stream);
+cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
+size_t resident_limit_bytes(int max_smem_optin);
 }
 namespace rt_strict {
-cudaError_t launch(const RtParams& P, int grid, bool count, cudaStream_t stream);
+cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
+size_t resident_limit_bytes(int max_smem_optin);
 }
 
 namespace {
@@ -105,6 +107,7 @@ struct rt_context {
     DevBuf<RtCameraDev> d_cams;
     DevBuf<uint8_t> d_out;
     DevBuf<RtCounters> d_cnt;
+    DevBuf<unsigned long long> d_tile;
     uint8_t* h_pinned = nullptr;
     size_t h_pinned_cap = 0;
     // uploaded scene
@@ -250,6 +253,7 @@ int rt_create(rt_context** out_ctx, int device) {
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) CU(cudaEventCreate(&c->ev[i]));
     CU(c->d_cnt.reserve(1));
+    CU(c->d_tile.reserve(2));
     *out_ctx = c;
     return RT_OK;
 }
@@ -260,7 +264,7 @@ int rt_destroy(rt_context* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->d_box_fast.release(); c->d_box_strict.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
-    c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release();
+    c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -368,6 +372,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.box_obj = c->d_box_obj.p; P.sph_obj = c->d_sph_obj.p;
     P.cold = c->d_cold.p; P.lights = c->d_lights.p; P.cams = c->d_cams.p;
     P.counters = c->d_cnt.p;
+    P.tile_counter = c->d_tile.p;
     P.n_box = c->n_box; P.n_sph = c->n_sph; P.n_lights = c->n_lights; P.max_depth = c->max_depth;
     P.n_frames = n_frames; P.width = width; P.height = height; P.y0 = y0; P.y1 = y1;
     P.spp = spp; P.seed = o.seed;
@@ -376,7 +381,8 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.spp_n = (n * n == spp) ? n : 0;
     P.tiles_x = (width + 7) / 8; P.tiles_y = (band_rows + 3) / 4;
     const size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : RT_BOX_F4_FAST) + P.n_sph) * 16;
-    P.resident = hot_bytes <= (size_t)(c->max_smem_optin / 2 - 2048) ? 1 : 0;
+    P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin)
+                                        : rt_fast::resident_limit_bytes(c->max_smem_optin)) ? 1 : 0;
 
     if (o.out_is_device) {
         P.out = (uint8_t*)out_rgba;
@@ -390,19 +396,18 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         P.out_row0 = y0;
     }
 
-    const long long n_tiles = (long long)P.tiles_x * P.tiles_y * n_frames;
-    long long want = (n_tiles + 7) / 8;
-    int grid = 2 * c->sm_count;
-    if (want < grid) grid = (int)(want > 0 ? want : 1);
+    const int grid = c->sm_count;   // the launcher sizes the persistent grid from the occupancy of the chosen kernel
 
     const bool count = o.stats != nullptr;
     if (count) CU(cudaMemsetAsync(c->d_cnt.p, 0, sizeof(RtCounters), st));
+    CU(cudaMemsetAsync(c->d_tile.p, 0, 2 * sizeof(unsigned long long), st));
     if (o.stats) CU(cudaEventRecord(c->ev[0], st));
     CU(o.strict ? rt_strict::launch(P, grid, false, st) : rt_fast::launch(P, grid, false, st));
     g_launches++;
     if (o.stats) CU(cudaEventRecord(c->ev[1], st));
     if (count) {
         // instrumented twin: same kernel with counters, run after the timed one (results identical)
+        CU(cudaMemsetAsync(c->d_tile.p, 0, 2 * sizeof(unsigned long long), st));
         CU(o.strict ? rt_strict::launch(P, grid, true, st) : rt_fast::launch(P, grid, true, st));
         g_launches++;
     }

@@ -48,6 +48,9 @@
 
 namespace RT_NS {
 
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 2
+#endif
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr unsigned kFull = 0xffffffffu;
@@ -146,18 +149,31 @@ __device__ __forceinline__ bool box_reject(float tn, float tf) { return !(tn < t
 __device__ __forceinline__ float box_pick(float tn, float tf) { return (tn < 0.0f) ? tf : tn; }
 
 // -------------------------------------------------------------------------
-// Ray / sphere test (glsl:585-625).  c = (centre, r*r).  Returns t (or <= 0 / NaN
-// for "no usable hit") and whether the origin is inside.
+// Ray / sphere test (glsl:585-625).  c = (centre, r*r).  Split like the box test:
+// the origin-dependent part (oc, qc) is shared by rays with a common origin.
+// Returns t (or <= 0 / NaN for "no usable hit") and whether the origin is inside.
 // -------------------------------------------------------------------------
-struct RayQ { float qa, iqa; };   // per-ray invariants of the quadratic (fast path)
+struct RayQ { float qa, iqa; };        // per-ray invariants of the quadratic (fast path)
+struct SphO { V3 oc; float qc; };      // per (origin, sphere)
+
+__device__ __forceinline__ RayQ ray_q(V3 d) {
+    RayQ q;
+    q.qa = __fmaf_rn(d.x, d.x, __fmaf_rn(d.y, d.y, __fmul_rn(d.z, d.z)));
+    q.iqa = 1.0f / q.qa;
+    return q;
+}
 
 #if RT_STRICT
-__device__ __forceinline__ float sphere_t(float4 c, V3 o, V3 d, RayQ, bool& inside) {
-    V3 oc = mk(o.x - c.x, o.y - c.y, o.z - c.z);
-    float qa = dot3(d, d);
-    float qb = dot3(2.0f * d, oc);
-    float qc = dot3(oc, oc) - c.w;
-    float qd = qb * qb - 4.0f * qa * qc;
+__device__ __forceinline__ SphO sphere_origin(float4 c, V3 o) {
+    SphO s;
+    s.oc = mk(o.x - c.x, o.y - c.y, o.z - c.z);          // r.start - o.position
+    s.qc = dot3(s.oc, s.oc) - c.w;                        // glsl:588
+    return s;
+}
+__device__ __forceinline__ float sphere_t(SphO so, V3 d, RayQ, bool& inside) {
+    float qa = dot3(d, d);                                // glsl:586
+    float qb = dot3(2.0f * d, so.oc);                     // glsl:587
+    float qd = qb * qb - 4.0f * qa * so.qc;               // glsl:591
     inside = false;
     if (qd < 0.0f) return -1.0f;
     float sq = sqrtf(qd);
@@ -169,11 +185,15 @@ __device__ __forceinline__ float sphere_t(float4 c, V3 o, V3 d, RayQ, bool& insi
     return tn;
 }
 #else
-__device__ __forceinline__ float sphere_t(float4 c, V3 o, V3 d, RayQ q, bool& inside) {
-    float ocx = o.x - c.x, ocy = o.y - c.y, ocz = o.z - c.z;
-    float hb = __fmaf_rn(d.x, ocx, __fmaf_rn(d.y, ocy, __fmul_rn(d.z, ocz)));       // qb / 2
-    float qc = __fmaf_rn(ocx, ocx, __fmaf_rn(ocy, ocy, __fmaf_rn(ocz, ocz, -c.w)));
-    float disc = __fmaf_rn(hb, hb, -__fmul_rn(q.qa, qc));                           // qd / 4
+__device__ __forceinline__ SphO sphere_origin(float4 c, V3 o) {
+    SphO s;
+    s.oc = mk(o.x - c.x, o.y - c.y, o.z - c.z);
+    s.qc = __fmaf_rn(s.oc.x, s.oc.x, __fmaf_rn(s.oc.y, s.oc.y, __fmaf_rn(s.oc.z, s.oc.z, -c.w)));
+    return s;
+}
+__device__ __forceinline__ float sphere_t(SphO so, V3 d, RayQ q, bool& inside) {
+    float hb = __fmaf_rn(d.x, so.oc.x, __fmaf_rn(d.y, so.oc.y, __fmul_rn(d.z, so.oc.z)));   // qb / 2
+    float disc = __fmaf_rn(hb, hb, -__fmul_rn(q.qa, so.qc));                                // qd / 4
     float sq = sqrt_approx(fmaxf(disc, 0.0f));
     float tn = __fmul_rn(-hb - sq, q.iqa);
     float tf = __fmul_rn(sq - hb, q.iqa);
@@ -183,44 +203,116 @@ __device__ __forceinline__ float sphere_t(float4 c, V3 o, V3 d, RayQ q, bool& in
 }
 #endif
 
-__device__ __forceinline__ RayQ ray_q(V3 d) {
-    RayQ q;
-    q.qa = __fmaf_rn(d.x, d.x, __fmaf_rn(d.y, d.y, __fmul_rn(d.z, d.z)));
-    q.iqa = 1.0f / q.qa;
-    return q;
+// -------------------------------------------------------------------------
+// Per-warp context: where this warp's object records come from, and its
+// shared-memory scratch.
+//   resident : the whole hot scene sits in the CTA's shared memory (staged once)
+//   streaming: the hot scene is larger than shared memory; each warp pulls
+//              kTileBox-record tiles through its own double buffer with TMA
+//              bulk copies (cp.async.bulk + mbarrier complete_tx), next tile in
+//              flight while the current one is tested.  Warps stay independent:
+//              no CTA barrier inside the object loop.
+// -------------------------------------------------------------------------
+constexpr int kTileBox = 64;                                   // boxes per tile
+constexpr int kTileBytes = kTileBox * RT_BOX_F4 * 16;
+constexpr int kTileSph = kTileBytes / 16;                      // spheres per tile
+constexpr int kRepackMinObjects = 48;                          // below this, shadow rays are never re-packed
+constexpr int kQueueRays = 64;                                 // compacted shadow-ray queue entries
+constexpr int kScratchBytes = kQueueRays * 8 * 4 + 96 * 4;     // queue + occlusion flags, per warp
+
+struct WarpCtx {
+    const float4* box_hot;       // resident: shared memory; streaming: global
+    const float4* sph_hot;
+    float* queue;                // [kQueueRays][8]
+    int* occ;                    // [96]
+    float4* buf[2];              // streaming double buffer (generic pointers)
+    uint32_t buf_addr[2];        // shared-space addresses of buf / barriers
+    uint32_t bar_addr[2];
+    uint32_t phase;              // bit b: parity to wait for on barrier b
+    int lane;
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ int n_box_tiles(const RtParams& P) { return (P.n_box + kTileBox - 1) / kTileBox; }
+__device__ __forceinline__ int n_sph_tiles(const RtParams& P) { return (P.n_sph + kTileSph - 1) / kTileSph; }
+
+// lane 0: start the bulk copy of tile t (boxes first, then spheres) into buffer t & 1
+__device__ __forceinline__ void tile_issue(const RtParams& P, WarpCtx& w, int t) {
+    const int nbt = n_box_tiles(P);
+    const void* src;
+    uint32_t bytes;
+    if (t < nbt) {
+        const int first = t * kTileBox, n = min(kTileBox, P.n_box - first);
+        src = w.box_hot + (size_t)first * RT_BOX_F4;
+        bytes = (uint32_t)n * RT_BOX_F4 * 16u;
+    } else {
+        const int first = (t - nbt) * kTileSph, n = min(kTileSph, P.n_sph - first);
+        src = w.sph_hot + first;
+        bytes = (uint32_t)n * 16u;
+    }
+    const int b = t & 1;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(w.bar_addr[b]), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(w.buf_addr[b]), "l"(src), "r"(bytes), "r"(w.bar_addr[b]) : "memory");
+}
+__device__ __forceinline__ void tile_wait(WarpCtx& w, int b) {
+    const uint32_t parity = (w.phase >> b) & 1u;
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(w.bar_addr[b]), "r"(parity) : "memory");
+    } while (!ok);
+    w.phase ^= 1u << b;
+}
+
+// Returns the records of tile t.  Streaming: waits for its copy and puts tile t+1 in flight.
+template <bool SMEM>
+__device__ __forceinline__ const float4* tile_acquire(const RtParams& P, WarpCtx& w, int t, int n_tiles) {
+    const int nbt = n_box_tiles(P);
+    if (SMEM) return t < nbt ? w.box_hot + (size_t)t * kTileBox * RT_BOX_F4 : w.sph_hot + (size_t)(t - nbt) * kTileSph;
+    __syncwarp();                                     // every lane is done reading buffer (t+1)&1 (tile t-1)
+    if (w.lane == 0 && t + 1 < n_tiles) tile_issue(P, w, t + 1);
+    tile_wait(w, t & 1);
+    return w.buf[t & 1];
+}
+template <bool SMEM>
+__device__ __forceinline__ void tile_begin(const RtParams& P, WarpCtx& w) {
+    if (!SMEM && w.lane == 0) tile_issue(P, w, 0);
+}
+// Early exit after tile t: the copy of tile t+1 is in flight; wait it out so the next trace starts clean.
+template <bool SMEM>
+__device__ __forceinline__ void tile_drain(WarpCtx& w, int t, int n_tiles) {
+    if (!SMEM && t + 1 < n_tiles) tile_wait(w, (t + 1) & 1);
 }
 
 // -------------------------------------------------------------------------
-// get_closest_collision (glsl:738-782) for R rays of this lane at once.
-// best[r] comes in as t_max (10000 for closest-hit rays, 1 for shadow rays,
-// 0 for an inactive slot) and goes out as the smallest accepted t; bidx[r] is
-// the hot-list position of the winner (boxes 0..n_box-1, spheres n_box..) or -1.
-// The loop trip count is warp-uniform.
-//   SHARED : all R rays start at o[0] (the shadow rays of one hit point,
-//            glsl:808) -> the origin is moved into the box frame once per box.
-//   ANYHIT : shadow semantics (glsl:816: in shadow iff closest t < 1, i.e. iff
-//            ANY object is hit at 0 < t < 1): no index, warp-vote early exit.
+// Brute-force loops over one tile (glsl:744-779).  Trip counts are warp-uniform.
+// best[r] comes in as t_max (10000 closest-hit, 1 shadow, 0 inactive slot) and goes
+// out as the smallest accepted t; bidx[r] = hot-list position of the winner
+// (boxes 0..n_box-1, spheres n_box..).
+//   SHARED : all R rays start at o[0] (the shadow rays of one hit point, glsl:808):
+//            the origin is moved into the primitive's frame once per primitive.
+//   ANYHIT : shadow semantics (glsl:816: in shadow iff ANY object is hit at 0 < t < 1).
 // Most tests miss, so the accept logic sits behind one warp vote per box.
 // -------------------------------------------------------------------------
-template <int R, bool SMEM, bool ANYHIT, bool SHARED, bool COUNT>
-__device__ __forceinline__ void trace(const RtParams& P, const float4* __restrict__ box_hot,
-                                      const float4* __restrict__ sph_hot,
-                                      const V3 (&o)[R], const V3 (&d)[R], float (&best)[R], int (&bidx)[R],
-                                      unsigned long long& n_box_tests, unsigned long long& n_sph_tests) {
-    const int n_box = P.n_box, n_sph = P.n_sph;
-    bool stop = false;
+template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+__device__ __forceinline__ void boxes_tile(const float4* __restrict__ recs, int n, int base,
+                                           const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                           float (&best)[kShadowBatch], int (&bidx)[kShadowBatch],
+                                           unsigned long long& n_tests) {
 #pragma unroll 2
-    for (int i = 0; i < n_box; ++i) {
+    for (int i = 0; i < n; ++i) {
         float4 rec[RT_BOX_F4];
 #pragma unroll
-        for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = SMEM ? box_hot[i * RT_BOX_F4 + k] : __ldg(box_hot + i * RT_BOX_F4 + k);
+        for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = recs[i * RT_BOX_F4 + k];
         float tn[R], tf[R];
         bool cand = false;
         V3 so;
         if (SHARED) so = box_origin(rec, o[0]);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (COUNT) n_box_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+            if (COUNT) n_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
             if (!SHARED) so = box_origin(rec, o[r]);
             Slabs s; V3 ld;
             box_slabs(rec, so, d[r], tn[r], tf[r], s, ld);
@@ -230,41 +322,189 @@ __device__ __forceinline__ void trace(const RtParams& P, const float4* __restric
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const float t = box_pick(tn[r], tf[r]);
-                if (!box_reject(tn[r], tf[r]) && t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = i; }
+                if (!box_reject(tn[r], tf[r]) && t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = base + i; }
             }
         }
-        if (ANYHIT && (i & 15) == 15) {
-            bool done = true;
-#pragma unroll
-            for (int r = 0; r < R; ++r) done = done && (best[r] < 1.0f);
-            if (__all_sync(kFull, done)) { stop = true; break; }
-        }
     }
-    if (ANYHIT && stop) return;
+}
 
+template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+__device__ __forceinline__ void spheres_tile(const RtParams& P, const float4* __restrict__ recs, int n, int base,
+                                             const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                             float (&best)[kShadowBatch], int (&bidx)[kShadowBatch],
+                                             unsigned long long& n_tests) {
     RayQ q[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) q[r] = ray_q(d[r]);
 #pragma unroll 2
-    for (int j = 0; j < n_sph; ++j) {
-        const float4 c = SMEM ? sph_hot[j] : __ldg(sph_hot + j);
+    for (int j = 0; j < n; ++j) {
+        const float4 c = recs[j];
+        SphO so;
+        if (SHARED) so = sphere_origin(c, o[0]);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (COUNT) n_sph_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+            if (COUNT) n_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+            if (!SHARED) so = sphere_origin(c, o[r]);
             bool inside;
-            float t = sphere_t(c, o[SHARED ? 0 : r], d[r], q[r], inside);
-            if (t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = n_box + j; }
-            else if (!ANYHIT && t == best[r] && bidx[r] >= 0 && bidx[r] < n_box) {
+            const float t = sphere_t(so, d[r], q[r], inside);
+            if (t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = P.n_box + base + j; }
+            else if (!ANYHIT && t == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
                 // exact tie with a box: the lower ORIGINAL index wins (glsl:773 strict '<' in index order)
-                if (__ldg(P.sph_obj + j) < __ldg(P.box_obj + bidx[r])) bidx[r] = n_box + j;
+                if (__ldg(P.sph_obj + base + j) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + j;
             }
         }
-        if (ANYHIT && (j & 15) == 15) {
-            bool done = true;
+    }
+}
+
+// One tile, dispatched on its kind.
+template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+__device__ __forceinline__ void any_tile(const RtParams& P, const float4* recs, int t,
+                                         const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                         float (&best)[kShadowBatch], int (&bidx)[kShadowBatch], RtCounters& cnt) {
+    const int nbt = n_box_tiles(P);
+    if (t < nbt) {
+        const int first = t * kTileBox;
+        boxes_tile<R, ANYHIT, SHARED, COUNT>(recs, min(kTileBox, P.n_box - first), first, o, d, best, bidx, cnt.box_tests);
+    } else {
+        const int first = (t - nbt) * kTileSph;
+        spheres_tile<R, ANYHIT, SHARED, COUNT>(P, recs, min(kTileSph, P.n_sph - first), first, o, d, best, bidx, cnt.sphere_tests);
+    }
+}
+
+// get_closest_collision (glsl:738-782) for one ray per lane.
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 o0, V3 d0, float& best0, int& bidx0,
+                                              RtCounters& cnt) {
+    V3 o[kShadowBatch], d[kShadowBatch];
+    float best[kShadowBatch]; int bidx[kShadowBatch];
+    o[0] = o0; d[0] = d0; best[0] = best0; bidx[0] = -1;
+    const int n_tiles = n_box_tiles(P) + n_sph_tiles(P);
+    tile_begin<SMEM>(P, w);
+    for (int t = 0; t < n_tiles; ++t) {
+        const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
+        any_tile<1, false, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+    }
+    best0 = best[0]; bidx0 = bidx[0];
+}
+
+// -------------------------------------------------------------------------
+// The shadow rays of one hit point per lane (glsl:807-819): common origin so,
+// directions sd[r] (light - p, un-normalised), sb[r] = 1 for a live slot, 0 for
+// an unused one.  On return sb[r] < 1 iff the ray is occluded.
+//
+// Starts as 3 rays per lane with the shared origin.  Rays drop out as soon as
+// ANY object occludes them, so at every tile boundary the warp counts its live
+// rays and, when they fit in fewer slots, re-packs them densely across the 32
+// lanes through a per-warp shared-memory queue (then 2, then 1 ray per lane, each
+// with its own origin).  Dead rays therefore stop costing issue slots, and a warp
+// whose rays are all occluded leaves the object loop.
+// -------------------------------------------------------------------------
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 so, const V3 (&sd)[kShadowBatch],
+                                             float (&sb)[kShadowBatch], RtCounters& cnt) {
+    V3 o[kShadowBatch], d[kShadowBatch];
+    float best[kShadowBatch]; int bidx[kShadowBatch]; int src[kShadowBatch];
 #pragma unroll
-            for (int r = 0; r < R; ++r) done = done && (best[r] < 1.0f);
-            if (__all_sync(kFull, done)) break;
+    for (int r = 0; r < kShadowBatch; ++r) { o[r] = so; d[r] = sd[r]; best[r] = sb[r]; bidx[r] = -1; src[r] = w.lane * kShadowBatch + r; }
+    int r_cur = kShadowBatch;
+    bool shared = true;
+    unsigned own_occ = 0u;
+    const unsigned lt_mask = (1u << w.lane) - 1u;
+    const int n_tiles = n_box_tiles(P) + n_sph_tiles(P);
+    bool started = false;
+
+    if (P.n_box + P.n_sph < kRepackMinObjects) {
+        // A handful of objects (the built-in scene has 5): the loop is shorter than one re-pack.
+        tile_begin<SMEM>(P, w);
+        for (int t = 0; t < n_tiles; ++t) {
+            const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
+            any_tile<kShadowBatch, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
         }
+#pragma unroll
+        for (int r = 0; r < kShadowBatch; ++r) sb[r] = best[r];
+        return;
+    }
+
+    for (int t = 0; t < n_tiles; ++t) {
+        // live rays of the warp, slot by slot
+        unsigned m[kShadowBatch];
+        int live = 0;
+#pragma unroll
+        for (int r = 0; r < kShadowBatch; ++r) {
+            m[r] = (r < r_cur) ? __ballot_sync(kFull, best[r] >= 1.0f) : 0u;
+            live += __popc(m[r]);
+        }
+        if (live == 0) {
+            if (started) tile_drain<SMEM>(w, t - 1, n_tiles);   // tile t is in flight
+            break;
+        }
+        const int new_r = (live + 31) >> 5;
+        if (new_r < r_cur) {
+            // ---- re-pack the live rays densely: queue entry = (origin, direction, source id) ----
+            if (shared) {
+#pragma unroll
+                for (int r = 0; r < kShadowBatch; ++r) {
+                    if (sb[r] >= 1.0f && best[r] < 1.0f) own_occ |= 1u << r;
+                    w.occ[w.lane * kShadowBatch + r] = 0;
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < kShadowBatch; ++r)
+                    if (r < r_cur && src[r] >= 0 && best[r] < 1.0f) w.occ[src[r]] = 1;
+            }
+            int base = 0;
+#pragma unroll
+            for (int r = 0; r < kShadowBatch; ++r) {
+                if (r < r_cur) {
+                    if (best[r] >= 1.0f) {
+                        float* q = w.queue + (base + __popc(m[r] & lt_mask)) * 8;
+                        const V3 oo = shared ? o[0] : o[r];
+                        *reinterpret_cast<float4*>(q) = make_float4(oo.x, oo.y, oo.z, d[r].x);
+                        *reinterpret_cast<float4*>(q + 4) = make_float4(d[r].y, d[r].z, __int_as_float(src[r]), 0.0f);
+                    }
+                    base += __popc(m[r]);
+                }
+            }
+            __syncwarp();
+#pragma unroll
+            for (int r = 0; r < kShadowBatch; ++r) {
+                const int idx = r * 32 + w.lane;
+                if (r < new_r && idx < live) {
+                    const float4 a = *reinterpret_cast<const float4*>(w.queue + idx * 8);
+                    const float4 b = *reinterpret_cast<const float4*>(w.queue + idx * 8 + 4);
+                    o[r] = mk(a.x, a.y, a.z); d[r] = mk(a.w, b.x, b.y); src[r] = __float_as_int(b.z);
+                    best[r] = 1.0f;
+                } else {
+                    o[r] = mk(0.0f, 0.0f, 0.0f); d[r] = mk(0.0f, 0.0f, 1.0f); src[r] = -1;
+                    best[r] = 0.0f;
+                }
+            }
+            __syncwarp();
+            r_cur = new_r;
+            shared = false;
+        }
+        if (!started) { tile_begin<SMEM>(P, w); started = true; }
+        const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
+        if (shared) any_tile<kShadowBatch, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+        else if (r_cur == 2) any_tile<2, true, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+        else any_tile<1, true, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+    }
+
+    if (shared) {
+#pragma unroll
+        for (int r = 0; r < kShadowBatch; ++r) sb[r] = best[r];
+    } else {
+        // holders report, owners collect
+#pragma unroll
+        for (int r = 0; r < kShadowBatch; ++r)
+            if (r < r_cur && src[r] >= 0 && best[r] < 1.0f) w.occ[src[r]] = 1;
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < kShadowBatch; ++r) {
+            const bool occluded = ((own_occ >> r) & 1u) || w.occ[w.lane * kShadowBatch + r] != 0;
+            if (sb[r] >= 1.0f) sb[r] = occluded ? 0.5f : 1.0f;
+        }
+        __syncwarp();
     }
 }
 
@@ -280,15 +520,15 @@ struct Hit {
 
 // Re-evaluates the winning primitive to produce p, n, inside (glsl:627-637 sphere,
 // glsl:686-721 box).  t is the value the trace loop accepted.
-template <bool SMEM>
-__device__ __forceinline__ Hit resolve_hit(const RtParams& P, const float4* __restrict__ box_hot,
-                                           const float4* __restrict__ sph_hot, V3 o, V3 d, float t, int bidx) {
+__device__ __forceinline__ Hit resolve_hit(const RtParams& P, const WarpCtx& w, V3 o, V3 d, float t, int bidx) {
+    const float4* box_hot = w.box_hot;      // shared memory (resident) or global (streaming): generic loads,
+    const float4* sph_hot = w.sph_hot;      // once per ray
     Hit h;
     if (bidx >= P.n_box) {
         const int j = bidx - P.n_box;
-        const float4 c = SMEM ? sph_hot[j] : __ldg(sph_hot + j);
+        const float4 c = sph_hot[j];
         bool inside;
-        (void)sphere_t(c, o, d, ray_q(d), inside);
+        (void)sphere_t(sphere_origin(c, o), d, ray_q(d), inside);
         h.obj = __ldg(P.sph_obj + j);
         h.inside = inside;
         h.p = o + t * d;                                            // glsl:628
@@ -300,7 +540,7 @@ __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const float4* __re
     const RtCold* __restrict__ c = P.cold + h.obj;
     float4 rec[RT_BOX_F4];
 #pragma unroll
-    for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = SMEM ? box_hot[bidx * RT_BOX_F4 + k] : __ldg(box_hot + bidx * RT_BOX_F4 + k);
+    for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = box_hot[bidx * RT_BOX_F4 + k];
     float tn, tf; Slabs s; V3 ld;
     box_slabs(rec, box_origin(rec, o), d, tn, tf, s, ld);
     h.inside = tn < 0.0f;                                           // glsl:690-696
@@ -309,14 +549,14 @@ __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const float4* __re
     if (t == by) face = 1;
     else if (t == bz) face = 2;
     // ray in the box's (unscaled) local space, as the shader computes it (glsl:655-656)
-    const float* w = c->w2l;
+    const float* m4 = c->w2l;
     V3 rs, rd;
-    rs.x = ((w[0] * o.x + w[1] * o.y) + w[2] * o.z) + w[3] * 1.0f;
-    rs.y = ((w[4] * o.x + w[5] * o.y) + w[6] * o.z) + w[7] * 1.0f;
-    rs.z = ((w[8] * o.x + w[9] * o.y) + w[10] * o.z) + w[11] * 1.0f;
-    rd.x = ((w[0] * d.x + w[1] * d.y) + w[2] * d.z) + w[3] * 0.0f;
-    rd.y = ((w[4] * d.x + w[5] * d.y) + w[6] * d.z) + w[7] * 0.0f;
-    rd.z = ((w[8] * d.x + w[9] * d.y) + w[10] * d.z) + w[11] * 0.0f;
+    rs.x = ((m4[0] * o.x + m4[1] * o.y) + m4[2] * o.z) + m4[3] * 1.0f;
+    rs.y = ((m4[4] * o.x + m4[5] * o.y) + m4[6] * o.z) + m4[7] * 1.0f;
+    rs.z = ((m4[8] * o.x + m4[9] * o.y) + m4[10] * o.z) + m4[11] * 1.0f;
+    rd.x = ((m4[0] * d.x + m4[1] * d.y) + m4[2] * d.z) + m4[3] * 0.0f;
+    rd.y = ((m4[4] * d.x + m4[5] * d.y) + m4[6] * d.z) + m4[7] * 0.0f;
+    rd.z = ((m4[8] * d.x + m4[9] * d.y) + m4[10] * d.z) + m4[11] * 0.0f;
     const float rdf = face == 0 ? rd.x : (face == 1 ? rd.y : rd.z);
     V3 nl = mk(face == 0 ? 1.0f : 0.0f, face == 1 ? 1.0f : 0.0f, face == 2 ? 1.0f : 0.0f);   // glsl:707-708
     if (rdf > 0.0f) nl = nl * -1.0f;                                // glsl:712-715
@@ -385,8 +625,7 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // All 32 lanes run the loop together; a lane without work rides along inactive.
 // -------------------------------------------------------------------------
 template <bool SMEM, bool COUNT>
-__device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __restrict__ box_hot,
-                                           const float4* __restrict__ sph_hot, bool valid, V3 org, V3 dir,
+__device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool valid, V3 org, V3 dir,
                                            RtCounters& cnt) {
     // pending rays: origin, direction, weight, remaining depth
     float stk[kStack][8];
@@ -403,21 +642,21 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
     while (__any_sync(kFull, sp > 0)) {
         const bool act = sp > 0;
         V3 o[1], d[1];
-        float w = 0.0f; int depth = 0;
+        float wgt = 0.0f; int depth = 0;
         float best[1]; int bidx[1];
         bidx[0] = -1;
         if (act) {
             --sp;
             o[0] = mk(stk[sp][0], stk[sp][1], stk[sp][2]);
             d[0] = mk(stk[sp][3], stk[sp][4], stk[sp][5]);
-            w = stk[sp][6]; depth = __float_as_int(stk[sp][7]);
+            wgt = stk[sp][6]; depth = __float_as_int(stk[sp][7]);
             best[0] = kFar;
         } else {
             o[0] = mk(0.0f, 0.0f, 0.0f); d[0] = mk(0.0f, 0.0f, 1.0f);
             best[0] = 0.0f;
         }
         // PHASE 0 (glsl:956-967)
-        trace<1, SMEM, false, false, COUNT>(P, box_hot, sph_hot, o, d, best, bidx, cnt.box_tests, cnt.sphere_tests);
+        trace_closest<SMEM, COUNT>(P, w, o[0], d[0], best[0], bidx[0], cnt);
         const bool hit = act && bidx[0] >= 0;
         if (COUNT && act) { cnt.rays++; cnt.nodes++; cnt.hit_nodes += hit; }
         if (act) iters += hit ? 6 : 1;
@@ -425,7 +664,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
         Hit h;
         const RtCold* __restrict__ mat = P.cold;
         if (hit) {
-            h = resolve_hit<SMEM>(P, box_hot, sph_hot, o[0], d[0], best[0], bidx[0]);
+            h = resolve_hit(P, w, o[0], d[0], best[0], bidx[0]);
             mat = P.cold + h.obj;
         }
         // PHASE 1: ads_phong_lighting (glsl:789-840), shadow rays kShadowBatch at a time
@@ -434,23 +673,22 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
         if (hit) view = normalize3(-d[0]);                          // glsl:827 normalize(-r.dir)
         if (__any_sync(kFull, hit)) {
             for (int l0 = 0; l0 < P.n_lights; l0 += kShadowBatch) {
-                V3 so[kShadowBatch], sd[kShadowBatch];
-                float sb[kShadowBatch]; int si[kShadowBatch];
+                V3 so = mk(0.0f, 0.0f, 0.0f), sd[kShadowBatch];
+                float sb[kShadowBatch];
+                if (hit) so = h.p + h.n * 0.01f;                                    // glsl:808
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     const int l = l0 + r;
-                    si[r] = -1;
                     if (hit && l < P.n_lights) {
                         const RtLightDev* __restrict__ L = P.lights + l;
-                        so[r] = h.p + h.n * 0.01f;                                  // glsl:808
                         sd[r] = mk(L->position[0] - h.p.x, L->position[1] - h.p.y, L->position[2] - h.p.z);  // glsl:809
                         sb[r] = 1.0f;                                               // glsl:816: shadowed iff closest t < 1
                     } else {
-                        so[r] = mk(0.0f, 0.0f, 0.0f); sd[r] = mk(0.0f, 0.0f, 1.0f);
+                        sd[r] = mk(0.0f, 0.0f, 1.0f);
                         sb[r] = 0.0f;
                     }
                 }
-                trace<kShadowBatch, SMEM, true, true, COUNT>(P, box_hot, sph_hot, so, sd, sb, si, cnt.box_tests, cnt.sphere_tests);
+                trace_shadow<SMEM, COUNT>(P, w, so, sd, sb, cnt);
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     const int l = l0 + r;
@@ -487,7 +725,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
             const float kr = mat->reflectivity, kt = mat->transparency;
             const bool reflected = depth > 0 && kr > 0.0f;
             const bool refracted = depth > 0 && kt > 0.0f;
-            float wp = w, wr = w * kr;
+            float wp = wgt, wr = wgt * kr;
             if (reflected) wp = wp * (1.0f - kr);
             if (refracted) { wp = wp * (1.0f - kt); wr = wr * (1.0f - kt); }
             color = color + wp * phong;
@@ -498,7 +736,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
                 const V3 rdv = refract3(d[0], h.n, ratio);
                 stk[sp][0] = ro.x; stk[sp][1] = ro.y; stk[sp][2] = ro.z;
                 stk[sp][3] = rdv.x; stk[sp][4] = rdv.y; stk[sp][5] = rdv.z;
-                stk[sp][6] = w * kt; stk[sp][7] = __int_as_float(depth - 1);
+                stk[sp][6] = wgt * kt; stk[sp][7] = __int_as_float(depth - 1);
                 ++sp;
             }
             if (reflected) {                                                                        // glsl:988-994
@@ -522,22 +760,50 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, const float4* __re
 // frames (tile index -> frame, tile row, tile column).
 // -------------------------------------------------------------------------
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(kThreads, 2) render_kernel(const __grid_constant__ RtParams P) {
+__global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const __grid_constant__ RtParams P) {
     extern __shared__ float4 smem_f4[];
-    const float4* box_hot = P.box_hot;
-    const float4* sph_hot = P.sph_hot;
+    // dynamic shared memory: [hot scene (resident only)] [per-warp scratch] [per-warp tile buffers + barriers (streaming only)]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpCtx w;
+    w.lane = lane;
+    w.phase = 0u;
+    size_t off4 = 0;                         // in float4 units
     if (SMEM) {
         // stage the hot scene once per CTA (persistent: once per SM-slot per launch)
         const int nb4 = P.n_box * RT_BOX_F4, ns4 = P.n_sph;
         for (int i = threadIdx.x; i < nb4; i += kThreads) smem_f4[i] = __ldg(P.box_hot + i);
         for (int i = threadIdx.x; i < ns4; i += kThreads) smem_f4[nb4 + i] = __ldg(P.sph_hot + i);
-        __syncthreads();
-        box_hot = smem_f4;
-        sph_hot = smem_f4 + nb4;
+        w.box_hot = smem_f4;
+        w.sph_hot = smem_f4 + nb4;
+        off4 = (size_t)nb4 + ns4;
+    } else {
+        w.box_hot = P.box_hot;
+        w.sph_hot = P.sph_hot;
     }
+    {
+        float4* scratch = smem_f4 + off4 + (size_t)warp * (kScratchBytes / 16);
+        w.queue = reinterpret_cast<float*>(scratch);
+        w.occ = reinterpret_cast<int*>(scratch + kQueueRays * 2);
+        off4 += (size_t)kWarps * (kScratchBytes / 16);
+    }
+    w.buf[0] = w.buf[1] = nullptr;
+    w.buf_addr[0] = w.buf_addr[1] = w.bar_addr[0] = w.bar_addr[1] = 0u;
+    if (!SMEM) {
+        float4* tiles = smem_f4 + off4 + (size_t)warp * (2 * kTileBytes / 16);
+        w.buf[0] = tiles; w.buf[1] = tiles + kTileBytes / 16;
+        off4 += (size_t)kWarps * (2 * kTileBytes / 16);
+        uint64_t* bars = reinterpret_cast<uint64_t*>(smem_f4 + off4) + warp * 2;
+        w.buf_addr[0] = smem_addr(w.buf[0]); w.buf_addr[1] = smem_addr(w.buf[1]);
+        w.bar_addr[0] = smem_addr(bars); w.bar_addr[1] = smem_addr(bars + 1);
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(w.bar_addr[0]) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(w.bar_addr[1]) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
+    __syncthreads();
 
-    const int lane = threadIdx.x & 31;
-    const int warp_global = blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const int warp_global = blockIdx.x * kWarps + warp;
     const int n_warps = gridDim.x * kWarps;
     const int tiles_per_frame = P.tiles_x * P.tiles_y;
     const long long n_tiles = (long long)tiles_per_frame * P.n_frames;
@@ -546,7 +812,10 @@ __global__ void __launch_bounds__(kThreads, 2) render_kernel(const __grid_consta
     RtCounters cnt;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = 0ull;
 
-    for (long long tile = warp_global; tile < n_tiles; tile += n_warps) {
+    // Work distribution: the first round of tiles is static (tile = global warp id); after that
+    // each warp pulls the next tile index from a global counter (zeroed by the host before the
+    // launch), so long and short tiles (glass vs wall, occluded vs open) even out.
+    for (long long tile = warp_global; tile < n_tiles;) {
         const int frame = (int)(tile / tiles_per_frame);
         const int tin = (int)(tile - (long long)frame * tiles_per_frame);
         const int ty = tin / P.tiles_x, tx = tin - ty * P.tiles_x;
@@ -561,7 +830,7 @@ __global__ void __launch_bounds__(kThreads, 2) render_kernel(const __grid_consta
             float jx, jy;
             jitter(P, px, py, s, jx, jy);
             const V3 dir = primary_dir(P, cam, px, py, jx, jy);
-            const V3 c = trace_sample<SMEM, COUNT>(P, box_hot, sph_hot, valid, org, dir, cnt);
+            const V3 c = trace_sample<SMEM, COUNT>(P, w, valid, org, dir, cnt);
             sum = sum + c;
         }
         const float fs = (float)P.spp;
@@ -583,6 +852,9 @@ __global__ void __launch_bounds__(kThreads, 2) render_kernel(const __grid_consta
         } else if (valid) {
             *reinterpret_cast<uint32_t*>(frame_out + pix * 4) = word;
         }
+        unsigned long long next = 0ull;
+        if (lane == 0) next = atomicAdd(P.tile_counter, 1ull);
+        tile = (long long)n_warps + (long long)__shfl_sync(kFull, next, 0);
     }
 
     if (COUNT) {
@@ -602,6 +874,9 @@ __global__ void __launch_bounds__(kThreads, 2) render_kernel(const __grid_consta
 // Launchers with C linkage-free, namespace-qualified names; called from rt_host.cpp.
 namespace RT_NS {
 inline size_t hot_smem_bytes(const RtParams& P) { return ((size_t)P.n_box * RT_BOX_F4 + (size_t)P.n_sph) * sizeof(float4); }
-cudaError_t launch(const RtParams& P, int grid, bool count, cudaStream_t stream);
+inline size_t scratch_smem_bytes() { return (size_t)kWarps * kScratchBytes; }
+inline size_t stream_smem_bytes() { return (size_t)kWarps * (2 * kTileBytes + 16); }
+size_t resident_limit_bytes(int max_smem_optin);
+cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
 }
