@@ -213,6 +213,10 @@ __device__ __forceinline__ float sphere_t(SphO so, V3 d, RayQ q, bool& inside) {
 //              flight while the current one is tested.  Warps stay independent:
 //              no CTA barrier inside the object loop.
 // -------------------------------------------------------------------------
+// All dynamic shared memory, addressed by float4 offset so that every record load is a plain LDS.128
+// (a generic pointer picked at run time would compile to generic LD).
+extern __shared__ float4 smem_f4[];
+
 constexpr int kTileBox = 64;                                   // boxes per tile
 constexpr int kTileBytes = kTileBox * RT_BOX_F4 * 16;
 constexpr int kTileSph = kTileBytes / 16;                      // spheres per tile
@@ -221,11 +225,10 @@ constexpr int kQueueRays = 64;                                 // compacted shad
 constexpr int kScratchBytes = kQueueRays * 8 * 4 + 96 * 4;     // queue + occlusion flags, per warp
 
 struct WarpCtx {
-    const float4* box_hot;       // resident: shared memory; streaming: global
-    const float4* sph_hot;
+    uint32_t box_off4, sph_off4; // resident: float4 offsets of the staged hot lists in smem_f4
     float* queue;                // [kQueueRays][8]
     int* occ;                    // [96]
-    float4* buf[2];              // streaming double buffer (generic pointers)
+    uint32_t buf_off4[2];        // streaming double buffer (float4 offsets in smem_f4)
     uint32_t buf_addr[2];        // shared-space addresses of buf / barriers
     uint32_t bar_addr[2];
     uint32_t phase;              // bit b: parity to wait for on barrier b
@@ -244,11 +247,11 @@ __device__ __forceinline__ void tile_issue(const RtParams& P, WarpCtx& w, int t)
     uint32_t bytes;
     if (t < nbt) {
         const int first = t * kTileBox, n = min(kTileBox, P.n_box - first);
-        src = w.box_hot + (size_t)first * RT_BOX_F4;
+        src = P.box_hot + (size_t)first * RT_BOX_F4;
         bytes = (uint32_t)n * RT_BOX_F4 * 16u;
     } else {
         const int first = (t - nbt) * kTileSph, n = min(kTileSph, P.n_sph - first);
-        src = w.sph_hot + first;
+        src = P.sph_hot + first;
         bytes = (uint32_t)n * 16u;
     }
     const int b = t & 1;
@@ -270,11 +273,11 @@ __device__ __forceinline__ void tile_wait(WarpCtx& w, int b) {
 template <bool SMEM>
 __device__ __forceinline__ const float4* tile_acquire(const RtParams& P, WarpCtx& w, int t, int n_tiles) {
     const int nbt = n_box_tiles(P);
-    if (SMEM) return t < nbt ? w.box_hot + (size_t)t * kTileBox * RT_BOX_F4 : w.sph_hot + (size_t)(t - nbt) * kTileSph;
+    if (SMEM) return smem_f4 + (t < nbt ? w.box_off4 + (uint32_t)t * kTileBox * RT_BOX_F4 : w.sph_off4 + (uint32_t)(t - nbt) * kTileSph);
     __syncwarp();                                     // every lane is done reading buffer (t+1)&1 (tile t-1)
     if (w.lane == 0 && t + 1 < n_tiles) tile_issue(P, w, t + 1);
     tile_wait(w, t & 1);
-    return w.buf[t & 1];
+    return smem_f4 + w.buf_off4[t & 1];
 }
 template <bool SMEM>
 __device__ __forceinline__ void tile_begin(const RtParams& P, WarpCtx& w) {
@@ -520,9 +523,11 @@ struct Hit {
 
 // Re-evaluates the winning primitive to produce p, n, inside (glsl:627-637 sphere,
 // glsl:686-721 box).  t is the value the trace loop accepted.
+template <bool SMEM>
 __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const WarpCtx& w, V3 o, V3 d, float t, int bidx) {
-    const float4* box_hot = w.box_hot;      // shared memory (resident) or global (streaming): generic loads,
-    const float4* sph_hot = w.sph_hot;      // once per ray
+    // the winner's hot record: shared memory when resident, global/L2 when streaming (once per ray)
+    const float4* box_hot = SMEM ? smem_f4 + w.box_off4 : P.box_hot;
+    const float4* sph_hot = SMEM ? smem_f4 + w.sph_off4 : P.sph_hot;
     Hit h;
     if (bidx >= P.n_box) {
         const int j = bidx - P.n_box;
@@ -664,7 +669,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
         Hit h;
         const RtCold* __restrict__ mat = P.cold;
         if (hit) {
-            h = resolve_hit(P, w, o[0], d[0], best[0], bidx[0]);
+            h = resolve_hit<SMEM>(P, w, o[0], d[0], best[0], bidx[0]);
             mat = P.cold + h.obj;
         }
         // PHASE 1: ads_phong_lighting (glsl:789-840), shadow rays kShadowBatch at a time
@@ -761,7 +766,6 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 // -------------------------------------------------------------------------
 template <bool SMEM, bool COUNT>
 __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const __grid_constant__ RtParams P) {
-    extern __shared__ float4 smem_f4[];
     // dynamic shared memory: [hot scene (resident only)] [per-warp scratch] [per-warp tile buffers + barriers (streaming only)]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpCtx w;
@@ -773,12 +777,11 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const _
         const int nb4 = P.n_box * RT_BOX_F4, ns4 = P.n_sph;
         for (int i = threadIdx.x; i < nb4; i += kThreads) smem_f4[i] = __ldg(P.box_hot + i);
         for (int i = threadIdx.x; i < ns4; i += kThreads) smem_f4[nb4 + i] = __ldg(P.sph_hot + i);
-        w.box_hot = smem_f4;
-        w.sph_hot = smem_f4 + nb4;
+        w.box_off4 = 0u;
+        w.sph_off4 = (uint32_t)nb4;
         off4 = (size_t)nb4 + ns4;
     } else {
-        w.box_hot = P.box_hot;
-        w.sph_hot = P.sph_hot;
+        w.box_off4 = w.sph_off4 = 0u;
     }
     {
         float4* scratch = smem_f4 + off4 + (size_t)warp * (kScratchBytes / 16);
@@ -786,14 +789,14 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const _
         w.occ = reinterpret_cast<int*>(scratch + kQueueRays * 2);
         off4 += (size_t)kWarps * (kScratchBytes / 16);
     }
-    w.buf[0] = w.buf[1] = nullptr;
+    w.buf_off4[0] = w.buf_off4[1] = 0u;
     w.buf_addr[0] = w.buf_addr[1] = w.bar_addr[0] = w.bar_addr[1] = 0u;
     if (!SMEM) {
-        float4* tiles = smem_f4 + off4 + (size_t)warp * (2 * kTileBytes / 16);
-        w.buf[0] = tiles; w.buf[1] = tiles + kTileBytes / 16;
+        w.buf_off4[0] = (uint32_t)(off4 + (size_t)warp * (2 * kTileBytes / 16));
+        w.buf_off4[1] = w.buf_off4[0] + kTileBytes / 16;
         off4 += (size_t)kWarps * (2 * kTileBytes / 16);
         uint64_t* bars = reinterpret_cast<uint64_t*>(smem_f4 + off4) + warp * 2;
-        w.buf_addr[0] = smem_addr(w.buf[0]); w.buf_addr[1] = smem_addr(w.buf[1]);
+        w.buf_addr[0] = smem_addr(smem_f4 + w.buf_off4[0]); w.buf_addr[1] = smem_addr(smem_f4 + w.buf_off4[1]);
         w.bar_addr[0] = smem_addr(bars); w.bar_addr[1] = smem_addr(bars + 1);
         if (lane == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(w.bar_addr[0]) : "memory");
