@@ -67,7 +67,19 @@ __device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y 
 __device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
 // Same association as the oracle's pinned dot(): ((x*x + y*y) + z*z)
 __device__ __forceinline__ float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+#if RT_STRICT
+// GLSL normalize / divide / pow exactly as the oracle pins them (IEEE sqrt and divide, libm-grade powf)
 __device__ __forceinline__ V3 normalize3(V3 v) { float l = sqrtf(dot3(v, v)); return mk(v.x / l, v.y / l, v.z / l); }
+__device__ __forceinline__ float fdiv(float a, float b) { return a / b; }
+__device__ __forceinline__ float fpow(float x, float y) { return powf(x, y); }
+#else
+// Shading-side arithmetic of the shipped kernel: v * rsqrt(v.v) (2 ulp), a * rcp(b) (2 ulp) and
+// exp2(y * log2(x)) with the accurate log2f / exp2f (not the fast-math intrinsics).  These sit
+// outside the hot loop but were ~40 % of the small-scene kernel's code size (instruction cache).
+__device__ __forceinline__ V3 normalize3(V3 v) { float r = rsqrtf(dot3(v, v)); return mk(v.x * r, v.y * r, v.z * r); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+__device__ __forceinline__ float fpow(float x, float y) { return (y == 0.0f) ? 1.0f : exp2f(y * log2f(x)); }
+#endif
 __device__ __forceinline__ V3 reflect3(V3 I, V3 N) { float d2 = 2.0f * dot3(N, I); return I - d2 * N; }
 __device__ __forceinline__ V3 refract3(V3 I, V3 N, float eta) {
     float ni = dot3(N, I);
@@ -402,7 +414,7 @@ __device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 
 // with its own origin).  Dead rays therefore stop costing issue slots, and a warp
 // whose rays are all occluded leaves the object loop.
 // -------------------------------------------------------------------------
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT>
 __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 so, const V3 (&sd)[kShadowBatch],
                                              float (&sb)[kShadowBatch], RtCounters& cnt) {
     V3 o[kShadowBatch], d[kShadowBatch];
@@ -416,8 +428,9 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
     const int n_tiles = n_box_tiles(P) + n_sph_tiles(P);
     bool started = false;
 
-    if (P.n_box + P.n_sph < kRepackMinObjects) {
+    if (!REPACK) {
         // A handful of objects (the built-in scene has 5): the loop is shorter than one re-pack.
+        // Chosen at launch (kRepackMinObjects); keeps the small-scene kernel small (instruction cache).
         tile_begin<SMEM>(P, w);
         for (int t = 0; t < n_tiles; ++t) {
             const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
@@ -613,8 +626,8 @@ __device__ __forceinline__ V3 primary_dir(const RtParams& P, const RtCameraDev* 
         s[r] = ((m[r] * vx + m[4 + r] * vy) + m[8 + r] * 0.5f) + m[12 + r] * 1.0f;
         e[r] = ((m[r] * vx + m[4 + r] * vy) + m[8 + r] * 1.0f) + m[12 + r] * 1.0f;
     }
-    V3 ws = mk(s[0] / s[3], s[1] / s[3], s[2] / s[3]);
-    V3 we = mk(e[0] / e[3], e[1] / e[3], e[2] / e[3]);
+    V3 ws = mk(fdiv(s[0], s[3]), fdiv(s[1], s[3]), fdiv(s[2], s[3]));
+    V3 we = mk(fdiv(e[0], e[3]), fdiv(e[1], e[3]), fdiv(e[2], e[3]));
     return normalize3(we - ws);
 }
 
@@ -629,7 +642,7 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // One sample: recursive_raytrace (glsl:1071-1105) as a weighted pending-ray stack.
 // All 32 lanes run the loop together; a lane without work rides along inactive.
 // -------------------------------------------------------------------------
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT>
 __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool valid, V3 org, V3 dir,
                                            RtCounters& cnt) {
     // pending rays: origin, direction, weight, remaining depth
@@ -693,7 +706,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                         sb[r] = 0.0f;
                     }
                 }
-                trace_shadow<SMEM, COUNT>(P, w, so, sd, sb, cnt);
+                trace_shadow<SMEM, REPACK, COUNT>(P, w, so, sd, sb, cnt);
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     const int l = l0 + r;
@@ -709,7 +722,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                             const float cos_theta = dot3(light_dir, h.n);                            // glsl:826
                             const float cos_phi = dot3(view, light_ref);                             // glsl:827
                             const float kd = fmaxf(cos_theta, 0.0f);
-                            const float ks = powf(fmaxf(cos_phi, 0.0f), mat->shininess);             // glsl:832
+                            const float ks = fpow(fmaxf(cos_phi, 0.0f), mat->shininess);             // glsl:832
 #pragma unroll
                             for (int k = 0; k < 4; ++k) {
                                 dif[k] += L->diffuse[k] * mat->diffuse[k] * kd;                      // glsl:830
@@ -764,7 +777,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 // The kernel.  grid = persistent CTAs; each warp walks 8x4-pixel tiles of all
 // frames (tile index -> frame, tile row, tile column).
 // -------------------------------------------------------------------------
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT>
 __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const __grid_constant__ RtParams P) {
     // dynamic shared memory: [hot scene (resident only)] [per-warp scratch] [per-warp tile buffers + barriers (streaming only)]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -833,11 +846,11 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const _
             float jx, jy;
             jitter(P, px, py, s, jx, jy);
             const V3 dir = primary_dir(P, cam, px, py, jx, jy);
-            const V3 c = trace_sample<SMEM, COUNT>(P, w, valid, org, dir, cnt);
+            const V3 c = trace_sample<SMEM, REPACK, COUNT>(P, w, valid, org, dir, cnt);
             sum = sum + c;
         }
         const float fs = (float)P.spp;
-        const V3 fc = mk(sum.x / fs, sum.y / fs, sum.z / fs);
+        const V3 fc = mk(fdiv(sum.x, fs), fdiv(sum.y, fs), fdiv(sum.z, fs));
         // vec4(final_color, 0.0) -> RGBA8 (glsl:404): R | G<<8 | B<<16 | A(=0)<<24
         const uint32_t word = unorm8(fc.x) | (unorm8(fc.y) << 8) | (unorm8(fc.z) << 16);
 
