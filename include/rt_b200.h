@@ -107,6 +107,8 @@ typedef struct rt_stats {
     uint64_t box_tests;       /* ray/box slab tests actually executed on the device */
     uint64_t sphere_tests;    /* ray/sphere tests actually executed on the device */
     uint64_t red_pixels;      /* samples that tripped the runaway guard (glsl:1098) */
+    uint64_t rays_not_traversed; /* shadow rays of `rays` whose outcome cannot change the pixel (zero-weight
+                                 surface, light without diffuse/specular) and that were not traversed */
     float kernel_ms;          /* CUDA-event time of the render kernel(s) of this call */
     float total_ms;           /* CUDA-event time incl. uploads and the D2H copy */
 } rt_stats;

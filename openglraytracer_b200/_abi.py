@@ -51,7 +51,7 @@ class Camera(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("nodes", C.c_uint64), ("hit_nodes", C.c_uint64),
                 ("shadow_rays", C.c_uint64), ("box_tests", C.c_uint64), ("sphere_tests", C.c_uint64),
-                ("red_pixels", C.c_uint64), ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
+                ("red_pixels", C.c_uint64), ("rays_not_traversed", C.c_uint64), ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

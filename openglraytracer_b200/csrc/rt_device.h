@@ -50,7 +50,7 @@ struct RtCold {
 };
 
 struct RtLightDev {
-    float position[4];
+    float position[4];  /* w = 1 if any diffuse/specular component is non-zero, else 0 */
     float ambient[4];
     float diffuse[4];
     float specular[4];
@@ -64,7 +64,7 @@ struct RtCameraDev {
 };
 
 struct RtCounters {
-    unsigned long long rays, nodes, hit_nodes, shadow_rays, box_tests, sphere_tests, red_pixels, pad;
+    unsigned long long rays, nodes, hit_nodes, shadow_rays, box_tests, sphere_tests, red_pixels, pad;   /* pad = shadow rays resolved without traversal */
 };
 
 struct RtParams {

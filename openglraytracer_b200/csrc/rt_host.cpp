@@ -199,6 +199,9 @@ int build_host_scene(const rt_scene* scene, HostScene* hs) {
         memcpy(d.ambient, L.ambient, 16);
         memcpy(d.diffuse, L.diffuse, 16);
         memcpy(d.specular, L.specular, 16);
+        bool lit = false;   // a light with zero diffuse and specular adds 0 shadowed or not (glsl:830-832)
+        for (int k = 0; k < 4; k++) lit = lit || L.diffuse[k] != 0.0f || L.specular[k] != 0.0f;
+        d.position[3] = lit ? 1.0f : 0.0f;
     }
     return RT_OK;
 }
@@ -432,6 +435,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         rt_stats* s = o.stats;
         s->rays = hc.rays; s->nodes = hc.nodes; s->hit_nodes = hc.hit_nodes; s->shadow_rays = hc.shadow_rays;
         s->box_tests = hc.box_tests; s->sphere_tests = hc.sphere_tests; s->red_pixels = hc.red_pixels;
+        s->rays_not_traversed = hc.pad;
         CU(cudaEventElapsedTime(&s->kernel_ms, c->ev[0], c->ev[1]));
         CU(cudaEventElapsedTime(&s->total_ms, c->ev[2], c->ev[3]));
     }

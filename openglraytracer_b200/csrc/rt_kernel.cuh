@@ -386,13 +386,27 @@ __device__ __forceinline__ void any_tile(const RtParams& P, const float4* recs, 
     }
 }
 
+// Small resident scene: both hot lists in one go, no tile bookkeeping.
+template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+__device__ __forceinline__ void all_objects(const RtParams& P, const WarpCtx& w,
+                                            const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                            float (&best)[kShadowBatch], int (&bidx)[kShadowBatch], RtCounters& cnt) {
+    boxes_tile<R, ANYHIT, SHARED, COUNT>(smem_f4 + w.box_off4, P.n_box, 0, o, d, best, bidx, cnt.box_tests);
+    spheres_tile<R, ANYHIT, SHARED, COUNT>(P, smem_f4 + w.sph_off4, P.n_sph, 0, o, d, best, bidx, cnt.sphere_tests);
+}
+
 // get_closest_collision (glsl:738-782) for one ray per lane.
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT>
 __device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 o0, V3 d0, float& best0, int& bidx0,
                                               RtCounters& cnt) {
     V3 o[kShadowBatch], d[kShadowBatch];
     float best[kShadowBatch]; int bidx[kShadowBatch];
     o[0] = o0; d[0] = d0; best[0] = best0; bidx[0] = -1;
+    if (SMEM && !REPACK) {
+        all_objects<1, false, false, COUNT>(P, w, o, d, best, bidx, cnt);
+        best0 = best[0]; bidx0 = bidx[0];
+        return;
+    }
     const int n_tiles = n_box_tiles(P) + n_sph_tiles(P);
     tile_begin<SMEM>(P, w);
     for (int t = 0; t < n_tiles; ++t) {
@@ -416,12 +430,12 @@ __device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 
 // -------------------------------------------------------------------------
 template <bool SMEM, bool REPACK, bool COUNT>
 __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 so, const V3 (&sd)[kShadowBatch],
-                                             float (&sb)[kShadowBatch], RtCounters& cnt) {
+                                             float (&sb)[kShadowBatch], int n_slots, RtCounters& cnt) {
     V3 o[kShadowBatch], d[kShadowBatch];
     float best[kShadowBatch]; int bidx[kShadowBatch]; int src[kShadowBatch];
 #pragma unroll
     for (int r = 0; r < kShadowBatch; ++r) { o[r] = so; d[r] = sd[r]; best[r] = sb[r]; bidx[r] = -1; src[r] = w.lane * kShadowBatch + r; }
-    int r_cur = kShadowBatch;
+    int r_cur = n_slots;           // slots in use: 1..3 with the shared origin, then 2 or 1 after a re-pack
     bool shared = true;
     unsigned own_occ = 0u;
     const unsigned lt_mask = (1u << w.lane) - 1u;
@@ -431,10 +445,17 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
     if (!REPACK) {
         // A handful of objects (the built-in scene has 5): the loop is shorter than one re-pack.
         // Chosen at launch (kRepackMinObjects); keeps the small-scene kernel small (instruction cache).
-        tile_begin<SMEM>(P, w);
-        for (int t = 0; t < n_tiles; ++t) {
-            const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
-            any_tile<kShadowBatch, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+        if (SMEM) {
+            // n_slots (1..3 rays per lane, warp-uniform) picks the loop: no issue slots for unused rays
+            if (n_slots == 3) all_objects<3, true, true, COUNT>(P, w, o, d, best, bidx, cnt);
+            else if (n_slots == 2) all_objects<2, true, true, COUNT>(P, w, o, d, best, bidx, cnt);
+            else all_objects<1, true, true, COUNT>(P, w, o, d, best, bidx, cnt);
+        } else {
+            tile_begin<SMEM>(P, w);
+            for (int t = 0; t < n_tiles; ++t) {
+                const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
+                any_tile<kShadowBatch, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+            }
         }
 #pragma unroll
         for (int r = 0; r < kShadowBatch; ++r) sb[r] = best[r];
@@ -501,8 +522,11 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
         }
         if (!started) { tile_begin<SMEM>(P, w); started = true; }
         const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
-        if (shared) any_tile<kShadowBatch, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
-        else if (r_cur == 2) any_tile<2, true, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+        if (shared) {
+            if (r_cur == 3) any_tile<3, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+            else if (r_cur == 2) any_tile<2, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+            else any_tile<1, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+        } else if (r_cur == 2) any_tile<2, true, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
         else any_tile<1, true, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
     }
 
@@ -674,7 +698,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             best[0] = 0.0f;
         }
         // PHASE 0 (glsl:956-967)
-        trace_closest<SMEM, COUNT>(P, w, o[0], d[0], best[0], bidx[0], cnt);
+        trace_closest<SMEM, REPACK, COUNT>(P, w, o[0], d[0], best[0], bidx[0], cnt);
         const bool hit = act && bidx[0] >= 0;
         if (COUNT && act) { cnt.rays++; cnt.nodes++; cnt.hit_nodes += hit; }
         if (act) iters += hit ? 6 : 1;
@@ -688,17 +712,58 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
         // PHASE 1: ads_phong_lighting (glsl:789-840), shadow rays kShadowBatch at a time
         float amb[4] = {0, 0, 0, 0}, dif[4] = {0, 0, 0, 0}, spc[4] = {0, 0, 0, 0};
         V3 view = mk(0.0f, 0.0f, 0.0f);
-        if (hit) view = normalize3(-d[0]);                          // glsl:827 normalize(-r.dir)
-        if (__any_sync(kFull, hit)) {
-            for (int l0 = 0; l0 < P.n_lights; l0 += kShadowBatch) {
+        // Bounce weights first (glsl:979-1054): final = mix(mix(phong, refl, kr), refr, kt) is linear in
+        // its three colours, so phong enters the pixel with the product weight wp.
+        float kr = 0.0f, kt = 0.0f, wp = 0.0f, wr = 0.0f;
+        bool reflected = false, refracted = false;
+        if (hit) {
+            kr = mat->reflectivity; kt = mat->transparency;
+            reflected = depth > 0 && kr > 0.0f;
+            refracted = depth > 0 && kt > 0.0f;
+            wp = wgt; wr = wgt * kr;
+            if (reflected) wp = wp * (1.0f - kr);
+            if (refracted) { wp = wp * (1.0f - kt); wr = wr * (1.0f - kt); }
+        }
+        // Dead-work elimination with identical results: a surface whose Phong colour enters with
+        // weight exactly 0 (a perfect mirror above depth 0: mix(phong, refl, 1.0)) needs neither
+        // lighting nor shadow rays; a light with all-zero diffuse and specular (the shader's "world
+        // ambient" light 0, glsl:202-207) adds 0 whether shadowed or not, so its shadow ray is not
+        // traversed.  The reference casts these rays; they are still COUNTED as rays (cnt.rays is the
+        // reference's ray count) and reported separately as not traversed.
+        const bool shade = hit && wp != 0.0f;
+        if (COUNT && hit && !shade) { cnt.rays += P.n_lights; cnt.shadow_rays += P.n_lights; cnt.pad += P.n_lights; }
+        if (shade) view = normalize3(-d[0]);                        // glsl:827 normalize(-r.dir)
+        if (__any_sync(kFull, shade)) {
+            // ambient term of every light, in light order (glsl:801)
+            for (int l = 0; l < P.n_lights; ++l) {
+                if (shade) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) amb[k] += P.lights[l].ambient[k] * mat->ambient[k];
+                    if (COUNT) { cnt.rays++; cnt.shadow_rays++; }
+                }
+            }
+            // shadow rays toward the lit lights, kShadowBatch at a time (the light list is warp-uniform)
+            int l = 0;
+            while (l < P.n_lights) {
+                int li[kShadowBatch];
+                int n_slots = 0;
+                while (l < P.n_lights && n_slots < kShadowBatch) {
+                    if (P.lights[l].position[3] != 0.0f) {
+                        if (n_slots == 0) li[0] = l; else if (n_slots == 1) li[1] = l; else li[2] = l;
+                        ++n_slots;
+                    } else if (COUNT && shade) {
+                        cnt.pad++;
+                    }
+                    ++l;
+                }
+                if (n_slots == 0) break;
                 V3 so = mk(0.0f, 0.0f, 0.0f), sd[kShadowBatch];
                 float sb[kShadowBatch];
-                if (hit) so = h.p + h.n * 0.01f;                                    // glsl:808
+                if (shade) so = h.p + h.n * 0.01f;                                  // glsl:808
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
-                    const int l = l0 + r;
-                    if (hit && l < P.n_lights) {
-                        const RtLightDev* __restrict__ L = P.lights + l;
+                    if (shade && r < n_slots) {
+                        const RtLightDev* __restrict__ L = P.lights + li[r];
                         sd[r] = mk(L->position[0] - h.p.x, L->position[1] - h.p.y, L->position[2] - h.p.z);  // glsl:809
                         sb[r] = 1.0f;                                               // glsl:816: shadowed iff closest t < 1
                     } else {
@@ -706,28 +771,21 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                         sb[r] = 0.0f;
                     }
                 }
-                trace_shadow<SMEM, REPACK, COUNT>(P, w, so, sd, sb, cnt);
+                trace_shadow<SMEM, REPACK, COUNT>(P, w, so, sd, sb, n_slots, cnt);
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
-                    const int l = l0 + r;
-                    if (hit && l < P.n_lights) {
-                        if (COUNT) { cnt.rays++; cnt.shadow_rays++; }
-                        const RtLightDev* __restrict__ L = P.lights + l;
+                    if (shade && r < n_slots && !(sb[r] < 1.0f)) {
+                        const RtLightDev* __restrict__ L = P.lights + li[r];
+                        const V3 light_dir = normalize3(sd[r]);                                  // glsl:804
+                        const V3 light_ref = normalize3(reflect3(-light_dir, h.n));              // glsl:825
+                        const float cos_theta = dot3(light_dir, h.n);                            // glsl:826
+                        const float cos_phi = dot3(view, light_ref);                             // glsl:827
+                        const float kd = fmaxf(cos_theta, 0.0f);
+                        const float ks = fpow(fmaxf(cos_phi, 0.0f), mat->shininess);             // glsl:832
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) amb[k] += L->ambient[k] * mat->ambient[k];     // glsl:801
-                        const bool in_shadow = sb[r] < 1.0f;
-                        if (!in_shadow) {
-                            const V3 light_dir = normalize3(sd[r]);                                  // glsl:804
-                            const V3 light_ref = normalize3(reflect3(-light_dir, h.n));              // glsl:825
-                            const float cos_theta = dot3(light_dir, h.n);                            // glsl:826
-                            const float cos_phi = dot3(view, light_ref);                             // glsl:827
-                            const float kd = fmaxf(cos_theta, 0.0f);
-                            const float ks = fpow(fmaxf(cos_phi, 0.0f), mat->shininess);             // glsl:832
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                dif[k] += L->diffuse[k] * mat->diffuse[k] * kd;                      // glsl:830
-                                spc[k] += L->specular[k] * mat->specular[k] * ks;                    // glsl:832
-                            }
+                        for (int k = 0; k < 4; ++k) {
+                            dif[k] += L->diffuse[k] * mat->diffuse[k] * kd;                      // glsl:830
+                            spc[k] += L->specular[k] * mat->specular[k] * ks;                    // glsl:832
                         }
                     }
                 }
@@ -738,15 +796,8 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 #pragma unroll
             for (int k = 0; k < 4; ++k) pc[k] = ((amb[k] + dif[k]) + spc[k]) + mat->emissive[k];    // glsl:837
             const V3 phong = mk(pc[0] * pc[3], pc[1] * pc[3], pc[2] * pc[3]);                        // glsl:839
-            // PHASES 2-4 (glsl:979-1054): final = mix(mix(phong, refl, kr), refr, kt) is linear in
-            // its three colours, so each child is pushed with its product weight.
-            const float kr = mat->reflectivity, kt = mat->transparency;
-            const bool reflected = depth > 0 && kr > 0.0f;
-            const bool refracted = depth > 0 && kt > 0.0f;
-            float wp = wgt, wr = wgt * kr;
-            if (reflected) wp = wp * (1.0f - kr);
-            if (refracted) { wp = wp * (1.0f - kt); wr = wr * (1.0f - kt); }
-            color = color + wp * phong;
+            if (shade) color = color + wp * phong;
+            // PHASES 2-3: each child ray is pushed with its product weight
             if (refracted) {                                                                        // glsl:1010-1027
                 const V3 ro = h.p - h.n * 0.001f;
                 float ratio = 1.0f / mat->refraction_index;
@@ -826,7 +877,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const _
     const int lx = lane & 7, ly = lane >> 3;
 
     RtCounters cnt;
-    cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = 0ull;
+    cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
 
     // Work distribution: the first round of tiles is static (tile = global warp id); after that
     // each warp pulls the next tile index from a global counter (zeroed by the host before the
@@ -875,9 +926,9 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const _
 
     if (COUNT) {
         // warp-reduce then one atomic per warp per counter
-        unsigned long long v[7] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests, cnt.red_pixels};
+        unsigned long long v[8] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests, cnt.red_pixels, cnt.pad};
 #pragma unroll
-        for (int k = 0; k < 7; ++k) {
+        for (int k = 0; k < 8; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

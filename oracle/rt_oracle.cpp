@@ -569,6 +569,7 @@ int oracle_render(const rt_scene* scene, const rt_camera* camera, uint8_t* out_r
                 out_index = (long)py * width + px;
             }
             vec3 sum(0.0f);
+            const uint64_t nodes_before = inv->st.nodes;
             for (int s = 0; s < spp; s++) {
                 // as written the shader rebuilds the camera matrices in every invocation
                 CameraMats m = as_written ? camera_mats(*camera) : frame_mats;
@@ -583,6 +584,7 @@ int oracle_render(const rt_scene* scene, const rt_camera* camera, uint8_t* out_r
             uint8_t* o = out_rgba + 4 * out_index;
             o[0] = unorm8(final_color.x); o[1] = unorm8(final_color.y); o[2] = unorm8(final_color.z);
             o[3] = unorm8(0.0f);
+            if (opts->out_nodes) opts->out_nodes[out_index] = (int32_t)(inv->st.nodes - nodes_before);
             if (opts->out_float) {
                 float* f = opts->out_float + 3 * out_index;
                 f[0] = final_color.x; f[1] = final_color.y; f[2] = final_color.z;

@@ -47,6 +47,7 @@ typedef struct oracle_options {
     int32_t n_pixels;
     float* out_float;       /* optional: pre-quantisation RGB, 3 floats per output pixel */
     oracle_stats* stats;    /* optional */
+    int32_t* out_nodes;     /* optional: bounce-tree nodes per output pixel (workload analysis) */
 } oracle_options;
 
 void oracle_options_default(oracle_options* o);

@@ -51,7 +51,8 @@ class OracleStats(C.Structure):
 class OracleOptions(C.Structure):
     _fields_ = [("spp", C.c_int32), ("seed", C.c_uint32), ("y0", C.c_int32), ("y1", C.c_int32),
                 ("as_written", C.c_int32), ("threads", C.c_int32), ("pixel_list", C.POINTER(C.c_int32)),
-                ("n_pixels", C.c_int32), ("out_float", C.POINTER(C.c_float)), ("stats", C.POINTER(OracleStats))]
+                ("n_pixels", C.c_int32), ("out_float", C.POINTER(C.c_float)), ("stats", C.POINTER(OracleStats)),
+                ("out_nodes", C.POINTER(C.c_int32))]
 
 
 _lib = None
@@ -118,7 +119,7 @@ def orbit_camera(speed):
 
 
 def render(scene, camera, width, height, spp=1, seed=0x5EED0001, y0=0, y1=0, as_written=False,
-           threads=0, pixels=None, want_float=False, want_stats=False):
+           threads=0, pixels=None, want_float=False, want_stats=False, want_nodes=False):
     """scene: SceneHolder-like (has .scene) or a Scene with the oracle's layout."""
     sc = scene.scene if hasattr(scene, "scene") else scene
     # accept the product binding's structs too (identical layout)
@@ -138,6 +139,9 @@ def render(scene, camera, width, height, spp=1, seed=0x5EED0001, y0=0, y1=0, as_
         fl = np.zeros((height, width, 3), np.float32)
     if want_float:
         opt.out_float = fl.ctypes.data_as(C.POINTER(C.c_float))
+    nodes = np.zeros(out.shape[:-1], np.int32)
+    if want_nodes:
+        opt.out_nodes = nodes.ctypes.data_as(C.POINTER(C.c_int32))
     st = OracleStats()
     if want_stats:
         opt.stats = C.pointer(st)
@@ -149,6 +153,8 @@ def render(scene, camera, width, height, spp=1, seed=0x5EED0001, y0=0, y1=0, as_
         res.append(fl)
     if want_stats:
         res.append(st.as_dict())
+    if want_nodes:
+        res.append(nodes)
     return res[0] if len(res) == 1 else tuple(res)
 
 
