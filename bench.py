@@ -322,7 +322,11 @@ def run_gpu(args, wl_name, wl):
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl_name, "scene": kind, "objects": n_obj, "width": w, "height": h, "spp": spp,
-                       "max_depth": depth, "rays_per_frame": rays_per_frame, "frames_per_step": world,
+                       "max_depth": depth, "rays_per_frame": rays_per_frame,
+                       "rays_traversed_per_frame": rays_per_frame - int(st["rays_not_traversed"]),
+                       "ray_unit": "one get_closest_collision call of the reference (glsl:738); shadow rays whose outcome "
+                                   "cannot change the pixel are counted but not traversed",
+                       "frames_per_step": world,
                        "parallelism": "frames sharded over %d GPU(s), no data-path collective" % world,
                        "l2": "flushed between timed steps (256 MiB write)", "kernel": "fast (fmad on, no fast-math)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": scene_bytes,

@@ -49,7 +49,10 @@
 namespace RT_NS {
 
 #ifndef RT_MIN_BLOCKS
-#define RT_MIN_BLOCKS 2
+#define RT_MIN_BLOCKS 2          // large scenes: the object loops are issue-bound, 16 warps/SM suffice
+#endif
+#ifndef RT_MIN_BLOCKS_SMALL
+#define RT_MIN_BLOCKS_SMALL 3    // small scenes: short loops, latency-bound shading -> 24 warps/SM
 #endif
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
@@ -829,7 +832,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 // frames (tile index -> frame, tile row, tile column).
 // -------------------------------------------------------------------------
 template <bool SMEM, bool REPACK, bool COUNT>
-__global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS) render_kernel(const __grid_constant__ RtParams P) {
+__global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOCKS_SMALL) render_kernel(const __grid_constant__ RtParams P) {
     // dynamic shared memory: [hot scene (resident only)] [per-warp scratch] [per-warp tile buffers + barriers (streaming only)]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpCtx w;
