@@ -111,6 +111,8 @@ typedef struct rt_stats {
                                  surface, light without diffuse/specular) and that were not traversed */
     float kernel_ms;          /* CUDA-event time of the render kernel(s) of this call */
     float total_ms;           /* CUDA-event time incl. uploads and the D2H copy */
+    uint64_t cull_tests;      /* bounding-sphere / discriminant tests executed for live rays (large scenes) */
+    uint64_t warp_iters;      /* bounce-loop iterations summed over warps; nodes/(32*warp_iters) = lane use */
 } rt_stats;
 
 /* Extended options; zero-initialise then override (rt_options_default()). The
@@ -127,6 +129,7 @@ typedef struct rt_options {
     int32_t async;            /* 1 = do not synchronise (device output only); pair with rt_synchronize() */
     void* stream;             /* cudaStream_t to launch on; NULL = the context's own stream */
     rt_stats* stats;          /* optional counters/timings */
+    int32_t no_cull;          /* 1 = large scenes run every slab test (no bounding-sphere test first); same image */
 } rt_options;
 
 typedef struct rt_context rt_context;

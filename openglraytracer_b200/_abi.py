@@ -51,7 +51,8 @@ class Camera(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("nodes", C.c_uint64), ("hit_nodes", C.c_uint64),
                 ("shadow_rays", C.c_uint64), ("box_tests", C.c_uint64), ("sphere_tests", C.c_uint64),
-                ("red_pixels", C.c_uint64), ("rays_not_traversed", C.c_uint64), ("kernel_ms", C.c_float), ("total_ms", C.c_float)]
+                ("red_pixels", C.c_uint64), ("rays_not_traversed", C.c_uint64), ("kernel_ms", C.c_float), ("total_ms", C.c_float),
+                ("cull_tests", C.c_uint64), ("warp_iters", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -61,7 +62,7 @@ class Options(C.Structure):
     _fields_ = [("spp", C.c_int32), ("seed", C.c_uint32), ("y0", C.c_int32), ("y1", C.c_int32),
                 ("out_is_device", C.c_int32), ("out_band_only", C.c_int32), ("device", C.c_int32),
                 ("strict", C.c_int32), ("async_", C.c_int32), ("stream", C.c_void_p),
-                ("stats", C.POINTER(Stats))]
+                ("stats", C.POINTER(Stats)), ("no_cull", C.c_int32)]
 
 
 # Every symbol include/rt_b200.h declares (tests check the library exports all of them).

@@ -157,13 +157,14 @@ class Raytracer:
         check(self._lib.rt_synchronize(self._ctx), "rt_synchronize")
 
     @staticmethod
-    def _options(spp, seed, y0, y1, strict, out_is_device, band_only, async_, stream, stats):
+    def _options(spp, seed, y0, y1, strict, out_is_device, band_only, async_, stream, stats, no_cull=False):
         o = Options()
         _abi.lib().rt_options_default(C.byref(o))
         o.spp, o.seed, o.y0, o.y1 = int(spp), int(seed), int(y0), int(y1)
         o.strict, o.out_is_device, o.out_band_only = int(strict), int(out_is_device), int(band_only)
         o.async_ = int(async_)
         o.stream = stream
+        o.no_cull = int(no_cull)
         if stats is not None:
             o.stats = C.pointer(stats)
         return o
@@ -175,7 +176,7 @@ class Raytracer:
 
     def render(self, scene, camera_uniforms, width, height, *, spp=1, seed=0x5EED0001, y0=0, y1=0,
                strict=False, out=None, out_device_ptr=None, band_only=False, async_=False, stream=None,
-               want_stats=False):
+               want_stats=False, no_cull=False):
         """Render one frame (camera_uniforms: Camera) or a batch (ctypes array of Camera).
 
         scene=None re-uses the last uploaded scene.  Host output: numpy uint8
@@ -190,7 +191,7 @@ class Raytracer:
         rows = (yy1 - max(y0, 0)) if band_only else height
         stats = Stats() if want_stats else None
         if out_device_ptr is not None:
-            opts = self._options(spp, seed, y0, y1, strict, 1, band_only, async_, stream, stats)
+            opts = self._options(spp, seed, y0, y1, strict, 1, band_only, async_, stream, stats, no_cull)
             target = C.c_void_p(int(out_device_ptr))
             result = None
         else:
@@ -198,7 +199,7 @@ class Raytracer:
                 out = np.empty((n, rows, width, 4) if batch else (rows, width, 4), np.uint8)
             if out.nbytes != n * rows * width * 4 or not out.flags["C_CONTIGUOUS"] or out.dtype != np.uint8:
                 raise ValueError("out must be a C-contiguous uint8 array of %d bytes" % (n * rows * width * 4))
-            opts = self._options(spp, seed, y0, y1, strict, 0, band_only, False, stream, stats)
+            opts = self._options(spp, seed, y0, y1, strict, 0, band_only, False, stream, stats, no_cull)
             target = C.c_void_p(out.ctypes.data)
             result = out
         if scene is not None:

@@ -65,10 +65,13 @@ struct RtCameraDev {
 
 struct RtCounters {
     unsigned long long rays, nodes, hit_nodes, shadow_rays, box_tests, sphere_tests, red_pixels, pad;   /* pad = shadow rays resolved without traversal */
+    unsigned long long cull_tests;   /* bounding-sphere tests executed for live rays (large-scene kernels) */
+    unsigned long long warp_iters;   /* bounce-loop iterations summed over warps: nodes / (32 * warp_iters) = lane utilisation */
 };
 
 struct RtParams {
     const float4* box_hot;
+    const float4* box_cull;     /* per box: (world-space centre, padded squared circumradius) */
     const float4* sph_hot;      /* (cx, cy, cz, r*r) */
     const int32_t* box_obj;     /* hot index -> original object index */
     const int32_t* sph_obj;
@@ -86,7 +89,7 @@ struct RtParams {
     uint32_t seed;
     int32_t tiles_x, tiles_y;   /* 8x4-pixel warp tiles covering width x (y1-y0) */
     int32_t resident;           /* 1: whole hot scene staged in shared memory once per CTA */
-    int32_t stream_tile;        /* boxes per streamed tile (streaming mode) */
+    int32_t cull;               /* 1: large-scene kernels run the slab test behind the bounding-sphere test */
 };
 
 #endif

@@ -85,6 +85,7 @@ struct DevBuf {
 
 struct HostScene {
     std::vector<float> box_fast, box_strict;   // float4 records
+    std::vector<float> box_cull;               // (world-space centre, padded squared circumradius) per box
     std::vector<float> sph;                    // (c, r*r)
     std::vector<int32_t> box_obj, sph_obj;
     std::vector<RtCold> cold;
@@ -100,7 +101,7 @@ struct rt_context {
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    DevBuf<float> d_box_fast, d_box_strict, d_sph;
+    DevBuf<float> d_box_fast, d_box_strict, d_box_cull, d_sph;
     DevBuf<int32_t> d_box_obj, d_sph_obj;
     DevBuf<RtCold> d_cold;
     DevBuf<RtLightDev> d_lights;
@@ -178,6 +179,20 @@ int build_host_scene(const rt_scene* scene, HostScene* hs) {
                     for (int k = 0; k < 3; k++) hs->box_fast.push_back((float)((double)c.w2l[4 * r + k] * ih));
                     hs->box_fast.push_back((float)(((double)c.w2l[4 * r + 3] - ctr) * ih));
                 }
+            }
+            // bounding sphere of the box in world space (T*R is rigid: the circumradius is |half extent|),
+            // padded by 1e-3 so that the test is conservative against the slab test's own rounding
+            {
+                double ctr[3], r2 = 0.0;
+                for (int r = 0; r < 3; r++) {
+                    ctr[r] = 0.5 * ((double)o.box_maxs[r] + (double)o.box_mins[r]);
+                    const double h = 0.5 * ((double)o.box_maxs[r] - (double)o.box_mins[r]);
+                    r2 += h * h;
+                }
+                for (int r = 0; r < 3; r++)
+                    hs->box_cull.push_back((float)((double)c.l2w[4 * r + 0] * ctr[0] + (double)c.l2w[4 * r + 1] * ctr[1] +
+                                                   (double)c.l2w[4 * r + 2] * ctr[2] + (double)c.l2w[4 * r + 3]));
+                hs->box_cull.push_back(degenerate ? -1e30f : (float)(r2 * 1.001 + 1e-12));
             }
         } else if (o.sphere_radius != -1.0f) {              // glsl:759
             c.kind = RT_KIND_SPHERE;
@@ -265,7 +280,7 @@ int rt_destroy(rt_context* c) {
     if (!c) return RT_OK;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->d_box_fast.release(); c->d_box_strict.release(); c->d_sph.release();
+    c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -304,6 +319,7 @@ int rt_upload_scene(rt_context* c, const rt_scene* scene) {
     CU(cudaStreamSynchronize(c->stream));
     CU(c->d_box_fast.reserve(hs.box_fast.size() + 4));
     CU(c->d_box_strict.reserve(hs.box_strict.size() + 4));
+    CU(c->d_box_cull.reserve(hs.box_cull.size() + 4));
     CU(c->d_sph.reserve(hs.sph.size() + 4));
     CU(c->d_box_obj.reserve(hs.box_obj.size() + 1));
     CU(c->d_sph_obj.reserve(hs.sph_obj.size() + 1));
@@ -315,6 +331,7 @@ int rt_upload_scene(rt_context* c, const rt_scene* scene) {
     };
     CU(up(c->d_box_fast.p, hs.box_fast.data(), hs.box_fast.size() * 4));
     CU(up(c->d_box_strict.p, hs.box_strict.data(), hs.box_strict.size() * 4));
+    CU(up(c->d_box_cull.p, hs.box_cull.data(), hs.box_cull.size() * 4));
     CU(up(c->d_sph.p, hs.sph.data(), hs.sph.size() * 4));
     CU(up(c->d_box_obj.p, hs.box_obj.data(), hs.box_obj.size() * 4));
     CU(up(c->d_sph_obj.p, hs.sph_obj.data(), hs.sph_obj.size() * 4));
@@ -371,6 +388,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     RtParams P;
     memset(&P, 0, sizeof(P));
     P.box_hot = reinterpret_cast<const float4*>(o.strict ? c->d_box_strict.p : c->d_box_fast.p);
+    P.box_cull = reinterpret_cast<const float4*>(c->d_box_cull.p);
     P.sph_hot = reinterpret_cast<const float4*>(c->d_sph.p);
     P.box_obj = c->d_box_obj.p; P.sph_obj = c->d_sph_obj.p;
     P.cold = c->d_cold.p; P.lights = c->d_lights.p; P.cams = c->d_cams.p;
@@ -383,7 +401,10 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     while ((n + 1) * (n + 1) <= spp) n++;
     P.spp_n = (n * n == spp) ? n : 0;
     P.tiles_x = (width + 7) / 8; P.tiles_y = (band_rows + 3) / 4;
-    const size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : RT_BOX_F4_FAST) + P.n_sph) * 16;
+    // Large scenes (fast kernel): the slab test runs behind a conservative bounding-sphere test, and
+    // only the 16-byte bounding-sphere records are staged / streamed (rt_kernel.cuh: boxes_tile_cull).
+    P.cull = (!o.strict && !o.no_cull) ? 1 : 0;
+    const size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : (P.cull ? 1 : RT_BOX_F4_FAST)) + P.n_sph) * 16;
     P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin)
                                         : rt_fast::resident_limit_bytes(c->max_smem_optin)) ? 1 : 0;
 
@@ -436,6 +457,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         s->rays = hc.rays; s->nodes = hc.nodes; s->hit_nodes = hc.hit_nodes; s->shadow_rays = hc.shadow_rays;
         s->box_tests = hc.box_tests; s->sphere_tests = hc.sphere_tests; s->red_pixels = hc.red_pixels;
         s->rays_not_traversed = hc.pad;
+        s->cull_tests = hc.cull_tests; s->warp_iters = hc.warp_iters;
         CU(cudaEventElapsedTime(&s->kernel_ms, c->ev[0], c->ev[1]));
         CU(cudaEventElapsedTime(&s->total_ms, c->ev[2], c->ev[3]));
     }

@@ -252,18 +252,24 @@ struct WarpCtx {
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ int n_box_tiles(const RtParams& P) { return (P.n_box + kTileBox - 1) / kTileBox; }
+// CULL: the box tiles hold 16-byte bounding-sphere records (kTileSph per tile); the 48-byte slab
+// records stay in global memory / L2 and are read only when some lane passes the bounding-sphere test.
+template <bool CULL> __device__ __forceinline__ constexpr int box_tile_n() { return CULL ? kTileSph : kTileBox; }
+template <bool CULL> __device__ __forceinline__ constexpr int box_tile_f4() { return CULL ? 1 : RT_BOX_F4; }
+template <bool CULL>
+__device__ __forceinline__ int n_box_tiles(const RtParams& P) { return (P.n_box + box_tile_n<CULL>() - 1) / box_tile_n<CULL>(); }
 __device__ __forceinline__ int n_sph_tiles(const RtParams& P) { return (P.n_sph + kTileSph - 1) / kTileSph; }
 
 // lane 0: start the bulk copy of tile t (boxes first, then spheres) into buffer t & 1
+template <bool CULL>
 __device__ __forceinline__ void tile_issue(const RtParams& P, WarpCtx& w, int t) {
-    const int nbt = n_box_tiles(P);
+    const int nbt = n_box_tiles<CULL>(P);
     const void* src;
     uint32_t bytes;
     if (t < nbt) {
-        const int first = t * kTileBox, n = min(kTileBox, P.n_box - first);
-        src = P.box_hot + (size_t)first * RT_BOX_F4;
-        bytes = (uint32_t)n * RT_BOX_F4 * 16u;
+        const int first = t * box_tile_n<CULL>(), n = min(box_tile_n<CULL>(), P.n_box - first);
+        src = CULL ? P.box_cull + first : P.box_hot + (size_t)first * RT_BOX_F4;
+        bytes = (uint32_t)n * box_tile_f4<CULL>() * 16u;
     } else {
         const int first = (t - nbt) * kTileSph, n = min(kTileSph, P.n_sph - first);
         src = P.sph_hot + first;
@@ -285,18 +291,18 @@ __device__ __forceinline__ void tile_wait(WarpCtx& w, int b) {
 }
 
 // Returns the records of tile t.  Streaming: waits for its copy and puts tile t+1 in flight.
-template <bool SMEM>
+template <bool SMEM, bool CULL>
 __device__ __forceinline__ const float4* tile_acquire(const RtParams& P, WarpCtx& w, int t, int n_tiles) {
-    const int nbt = n_box_tiles(P);
-    if (SMEM) return smem_f4 + (t < nbt ? w.box_off4 + (uint32_t)t * kTileBox * RT_BOX_F4 : w.sph_off4 + (uint32_t)(t - nbt) * kTileSph);
+    const int nbt = n_box_tiles<CULL>(P);
+    if (SMEM) return smem_f4 + (t < nbt ? w.box_off4 + (uint32_t)t * box_tile_n<CULL>() * box_tile_f4<CULL>() : w.sph_off4 + (uint32_t)(t - nbt) * kTileSph);
     __syncwarp();                                     // every lane is done reading buffer (t+1)&1 (tile t-1)
-    if (w.lane == 0 && t + 1 < n_tiles) tile_issue(P, w, t + 1);
+    if (w.lane == 0 && t + 1 < n_tiles) tile_issue<CULL>(P, w, t + 1);
     tile_wait(w, t & 1);
     return smem_f4 + w.buf_off4[t & 1];
 }
-template <bool SMEM>
+template <bool SMEM, bool CULL>
 __device__ __forceinline__ void tile_begin(const RtParams& P, WarpCtx& w) {
-    if (!SMEM && w.lane == 0) tile_issue(P, w, 0);
+    if (!SMEM && w.lane == 0) tile_issue<CULL>(P, w, 0);
 }
 // Early exit after tile t: the copy of tile t+1 is in flight; wait it out so the next trace starts clean.
 template <bool SMEM>
@@ -346,14 +352,147 @@ __device__ __forceinline__ void boxes_tile(const float4* __restrict__ recs, int 
     }
 }
 
+// -------------------------------------------------------------------------
+// Boxes behind a conservative bounding-sphere test (large scenes).
+// recs[i] = (centre of box base+i in world space, padded squared circumradius).  A ray's LINE
+// misses that sphere iff hb^2 < qa*qc (negative discriminant); the slab test of glsl:655-680 can
+// only succeed for a line that meets the box, hence its circumsphere, so skipping it then changes
+// nothing.  The radius is padded by 1e-3 (relative, host prologue) and qa by 1e-4, orders of
+// magnitude more than the FP32 rounding of either test, so the decision is conservative and the
+// image is byte-identical with the test on or off (tests/test_gpu_parity.py).  Still brute force:
+// every ray meets every object (glsl:744), in original order.  Cost: 5 FP32 instructions per
+// (ray, box) instead of 21; the 48-byte slab record is read from global/L2 only behind the vote.
+// -------------------------------------------------------------------------
+// The slab test of box `idx` for the rays whose bit is set in pm (rare path, kept out of the unrolled loop).
 template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+__device__ __forceinline__ void box_full_test(const RtParams& P, int idx, unsigned pm,
+                                              const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                              float (&best)[kShadowBatch], int (&bidx)[kShadowBatch], RtCounters& cnt) {
+    const float4* __restrict__ g = P.box_hot + (size_t)idx * RT_BOX_F4;
+    float4 rec[RT_BOX_F4];
+#pragma unroll
+    for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = __ldg(g + k);
+    V3 bo;
+    if (SHARED) bo = box_origin(rec, o[0]);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const bool mine = (pm >> r) & 1u;
+        if (COUNT) cnt.box_tests += mine;
+        if (!SHARED) bo = box_origin(rec, o[r]);
+        float tn, tf; Slabs s; V3 ld;
+        box_slabs(rec, bo, d[r], tn, tf, s, ld);
+        const float t = box_pick(tn, tf);
+        // `mine` keeps the outcome a function of the ray alone (not of which lanes share its warp)
+        if (mine && !box_reject(tn, tf) && t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = idx; }
+    }
+}
+
+template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+__device__ __forceinline__ void boxes_tile_cull(const RtParams& P, const float4* __restrict__ recs, int n, int base,
+                                                const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                                float (&best)[kShadowBatch], int (&bidx)[kShadowBatch],
+                                                RtCounters& cnt) {
+    constexpr int G = 4;                 // boxes per warp vote
+    float qe[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        qe[r] = __fmul_rn(__fmaf_rn(d[r].x, d[r].x, __fmaf_rn(d[r].y, d[r].y, __fmul_rn(d[r].z, d[r].z))), 0.9999f);
+    for (int i = 0; i < n; i += G) {
+        // Fast path: G boxes, one predicate, one vote.  A ray that is no longer live (occluded shadow
+        // ray, idle lane) gets qa = 1e30 so that it fails the test unless its origin lies inside the
+        // sphere; the slow path below re-checks liveness exactly, so that only costs a rare detour.
+        float qf[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool live = ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+            if (COUNT) cnt.cull_tests += live ? (unsigned long long)min(G, n - i) : 0ull;
+            qf[r] = live ? qe[r] : 1e30f;
+        }
+        bool any = false;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            // a record past n (the buffers are padded to a multiple of G records) can only cause a detour
+            const float4 c = recs[i + g];
+            SphO so;
+            if (SHARED) so = sphere_origin(c, o[0]);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (!SHARED) so = sphere_origin(c, o[r]);
+                const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qf[r], so.qc));
+                any = any || disc >= 0.0f;
+            }
+        }
+        if (__any_sync(kFull, any)) {
+            // Slow path (about one group in ten): redo the G tests one box at a time, exactly.
+#pragma unroll 1
+            for (int g = 0; g < G && i + g < n; ++g) {
+                const float4 c = recs[i + g];
+                unsigned m = 0u;
+                SphO so;
+                if (SHARED) so = sphere_origin(c, o[0]);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if (!SHARED) so = sphere_origin(c, o[r]);
+                    const bool live = ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+                    const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                    const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qe[r], so.qc));
+                    if (live && disc >= 0.0f) m |= 1u << r;
+                }
+                if (__any_sync(kFull, m != 0u))
+                    box_full_test<R, ANYHIT, SHARED, COUNT>(P, base + i + g, m, o, d, best, bidx, cnt);
+            }
+        }
+    }
+}
+
+template <int R, bool ANYHIT, bool SHARED, bool COUNT, bool CULL>
 __device__ __forceinline__ void spheres_tile(const RtParams& P, const float4* __restrict__ recs, int n, int base,
                                              const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
                                              float (&best)[kShadowBatch], int (&bidx)[kShadowBatch],
-                                             unsigned long long& n_tests) {
+                                             RtCounters& cnt) {
     RayQ q[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) q[r] = ray_q(d[r]);
+#if !RT_STRICT
+    if (CULL) {
+        // Large scenes: the discriminant of glsl:591 first (5 FP32 instructions per ray); the roots
+        // are computed only when some lane of the warp has a non-negative one.  Same expressions as
+        // sphere_t(), evaluated in two steps, so the result is identical.
+#pragma unroll 4
+        for (int j = 0; j < n; ++j) {
+            const float4 c = recs[j];
+            SphO so;
+            if (SHARED) so = sphere_origin(c, o[0]);
+            float hb[R], disc[R];
+            bool any = false;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (!SHARED) so = sphere_origin(c, o[r]);
+                const bool live = ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+                if (COUNT) cnt.cull_tests += live;
+                hb[r] = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                disc[r] = __fmaf_rn(hb[r], hb[r], -__fmul_rn(q[r].qa, so.qc));
+                any = any || (live && disc[r] >= 0.0f);
+            }
+            if (__any_sync(kFull, any)) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    if (COUNT) cnt.sphere_tests += (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) && disc[r] >= 0.0f;
+                    const float sq = sqrt_approx(fmaxf(disc[r], 0.0f));
+                    const float tn = __fmul_rn(-hb[r] - sq, q[r].iqa);
+                    const float tf = __fmul_rn(sq - hb[r], q[r].iqa);
+                    const float t = (disc[r] < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
+                    if (t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = P.n_box + base + j; }
+                    else if (!ANYHIT && t == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
+                        if (__ldg(P.sph_obj + base + j) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + j;
+                    }
+                }
+            }
+        }
+        return;
+    }
+#endif
 #pragma unroll 2
     for (int j = 0; j < n; ++j) {
         const float4 c = recs[j];
@@ -361,7 +500,7 @@ __device__ __forceinline__ void spheres_tile(const RtParams& P, const float4* __
         if (SHARED) so = sphere_origin(c, o[0]);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (COUNT) n_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+            if (COUNT) cnt.sphere_tests += ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
             if (!SHARED) so = sphere_origin(c, o[r]);
             bool inside;
             const float t = sphere_t(so, d[r], q[r], inside);
@@ -375,17 +514,19 @@ __device__ __forceinline__ void spheres_tile(const RtParams& P, const float4* __
 }
 
 // One tile, dispatched on its kind.
-template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+template <int R, bool ANYHIT, bool SHARED, bool COUNT, bool CULL>
 __device__ __forceinline__ void any_tile(const RtParams& P, const float4* recs, int t,
                                          const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
                                          float (&best)[kShadowBatch], int (&bidx)[kShadowBatch], RtCounters& cnt) {
-    const int nbt = n_box_tiles(P);
+    const int nbt = n_box_tiles<CULL>(P);
     if (t < nbt) {
-        const int first = t * kTileBox;
-        boxes_tile<R, ANYHIT, SHARED, COUNT>(recs, min(kTileBox, P.n_box - first), first, o, d, best, bidx, cnt.box_tests);
+        const int first = t * box_tile_n<CULL>();
+        const int n = min(box_tile_n<CULL>(), P.n_box - first);
+        if (CULL) boxes_tile_cull<R, ANYHIT, SHARED, COUNT>(P, recs, n, first, o, d, best, bidx, cnt);
+        else boxes_tile<R, ANYHIT, SHARED, COUNT>(recs, n, first, o, d, best, bidx, cnt.box_tests);
     } else {
         const int first = (t - nbt) * kTileSph;
-        spheres_tile<R, ANYHIT, SHARED, COUNT>(P, recs, min(kTileSph, P.n_sph - first), first, o, d, best, bidx, cnt.sphere_tests);
+        spheres_tile<R, ANYHIT, SHARED, COUNT, CULL>(P, recs, min(kTileSph, P.n_sph - first), first, o, d, best, bidx, cnt);
     }
 }
 
@@ -395,11 +536,11 @@ __device__ __forceinline__ void all_objects(const RtParams& P, const WarpCtx& w,
                                             const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
                                             float (&best)[kShadowBatch], int (&bidx)[kShadowBatch], RtCounters& cnt) {
     boxes_tile<R, ANYHIT, SHARED, COUNT>(smem_f4 + w.box_off4, P.n_box, 0, o, d, best, bidx, cnt.box_tests);
-    spheres_tile<R, ANYHIT, SHARED, COUNT>(P, smem_f4 + w.sph_off4, P.n_sph, 0, o, d, best, bidx, cnt.sphere_tests);
+    spheres_tile<R, ANYHIT, SHARED, COUNT, false>(P, smem_f4 + w.sph_off4, P.n_sph, 0, o, d, best, bidx, cnt);
 }
 
 // get_closest_collision (glsl:738-782) for one ray per lane.
-template <bool SMEM, bool REPACK, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
 __device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 o0, V3 d0, float& best0, int& bidx0,
                                               RtCounters& cnt) {
     V3 o[kShadowBatch], d[kShadowBatch];
@@ -410,11 +551,11 @@ __device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 
         best0 = best[0]; bidx0 = bidx[0];
         return;
     }
-    const int n_tiles = n_box_tiles(P) + n_sph_tiles(P);
-    tile_begin<SMEM>(P, w);
+    const int n_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
+    tile_begin<SMEM, CULL>(P, w);
     for (int t = 0; t < n_tiles; ++t) {
-        const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
-        any_tile<1, false, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+        const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_tiles);
+        any_tile<1, false, false, COUNT, CULL>(P, recs, t, o, d, best, bidx, cnt);
     }
     best0 = best[0]; bidx0 = bidx[0];
 }
@@ -431,7 +572,7 @@ __device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 
 // with its own origin).  Dead rays therefore stop costing issue slots, and a warp
 // whose rays are all occluded leaves the object loop.
 // -------------------------------------------------------------------------
-template <bool SMEM, bool REPACK, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
 __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 so, const V3 (&sd)[kShadowBatch],
                                              float (&sb)[kShadowBatch], int n_slots, RtCounters& cnt) {
     V3 o[kShadowBatch], d[kShadowBatch];
@@ -442,7 +583,7 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
     bool shared = true;
     unsigned own_occ = 0u;
     const unsigned lt_mask = (1u << w.lane) - 1u;
-    const int n_tiles = n_box_tiles(P) + n_sph_tiles(P);
+    const int n_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
     bool started = false;
 
     if (!REPACK) {
@@ -454,10 +595,10 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
             else if (n_slots == 2) all_objects<2, true, true, COUNT>(P, w, o, d, best, bidx, cnt);
             else all_objects<1, true, true, COUNT>(P, w, o, d, best, bidx, cnt);
         } else {
-            tile_begin<SMEM>(P, w);
+            tile_begin<SMEM, CULL>(P, w);
             for (int t = 0; t < n_tiles; ++t) {
-                const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
-                any_tile<kShadowBatch, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+                const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_tiles);
+                any_tile<kShadowBatch, true, true, COUNT, CULL>(P, recs, t, o, d, best, bidx, cnt);
             }
         }
 #pragma unroll
@@ -523,14 +664,14 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
             r_cur = new_r;
             shared = false;
         }
-        if (!started) { tile_begin<SMEM>(P, w); started = true; }
-        const float4* recs = tile_acquire<SMEM>(P, w, t, n_tiles);
+        if (!started) { tile_begin<SMEM, CULL>(P, w); started = true; }
+        const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_tiles);
         if (shared) {
-            if (r_cur == 3) any_tile<3, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
-            else if (r_cur == 2) any_tile<2, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
-            else any_tile<1, true, true, COUNT>(P, recs, t, o, d, best, bidx, cnt);
-        } else if (r_cur == 2) any_tile<2, true, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
-        else any_tile<1, true, false, COUNT>(P, recs, t, o, d, best, bidx, cnt);
+            if (r_cur == 3) any_tile<3, true, true, COUNT, CULL>(P, recs, t, o, d, best, bidx, cnt);
+            else if (r_cur == 2) any_tile<2, true, true, COUNT, CULL>(P, recs, t, o, d, best, bidx, cnt);
+            else any_tile<1, true, true, COUNT, CULL>(P, recs, t, o, d, best, bidx, cnt);
+        } else if (r_cur == 2) any_tile<2, true, false, COUNT, CULL>(P, recs, t, o, d, best, bidx, cnt);
+        else any_tile<1, true, false, COUNT, CULL>(P, recs, t, o, d, best, bidx, cnt);
     }
 
     if (shared) {
@@ -563,10 +704,10 @@ struct Hit {
 
 // Re-evaluates the winning primitive to produce p, n, inside (glsl:627-637 sphere,
 // glsl:686-721 box).  t is the value the trace loop accepted.
-template <bool SMEM>
+template <bool SMEM, bool CULL>
 __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const WarpCtx& w, V3 o, V3 d, float t, int bidx) {
     // the winner's hot record: shared memory when resident, global/L2 when streaming (once per ray)
-    const float4* box_hot = SMEM ? smem_f4 + w.box_off4 : P.box_hot;
+    const float4* box_hot = (SMEM && !CULL) ? smem_f4 + w.box_off4 : P.box_hot;
     const float4* sph_hot = SMEM ? smem_f4 + w.sph_off4 : P.sph_hot;
     Hit h;
     if (bidx >= P.n_box) {
@@ -669,7 +810,7 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // One sample: recursive_raytrace (glsl:1071-1105) as a weighted pending-ray stack.
 // All 32 lanes run the loop together; a lane without work rides along inactive.
 // -------------------------------------------------------------------------
-template <bool SMEM, bool REPACK, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
 __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool valid, V3 org, V3 dir,
                                            RtCounters& cnt) {
     // pending rays: origin, direction, weight, remaining depth
@@ -701,15 +842,16 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             best[0] = 0.0f;
         }
         // PHASE 0 (glsl:956-967)
-        trace_closest<SMEM, REPACK, COUNT>(P, w, o[0], d[0], best[0], bidx[0], cnt);
+        trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, o[0], d[0], best[0], bidx[0], cnt);
         const bool hit = act && bidx[0] >= 0;
         if (COUNT && act) { cnt.rays++; cnt.nodes++; cnt.hit_nodes += hit; }
+        if (COUNT) cnt.warp_iters++;
         if (act) iters += hit ? 6 : 1;
 
         Hit h;
         const RtCold* __restrict__ mat = P.cold;
         if (hit) {
-            h = resolve_hit<SMEM>(P, w, o[0], d[0], best[0], bidx[0]);
+            h = resolve_hit<SMEM, CULL>(P, w, o[0], d[0], best[0], bidx[0]);
             mat = P.cold + h.obj;
         }
         // PHASE 1: ads_phong_lighting (glsl:789-840), shadow rays kShadowBatch at a time
@@ -774,7 +916,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                         sb[r] = 0.0f;
                     }
                 }
-                trace_shadow<SMEM, REPACK, COUNT>(P, w, so, sd, sb, n_slots, cnt);
+                trace_shadow<SMEM, REPACK, COUNT, CULL>(P, w, so, sd, sb, n_slots, cnt);
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     if (shade && r < n_slots && !(sb[r] < 1.0f)) {
@@ -831,7 +973,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 // The kernel.  grid = persistent CTAs; each warp walks 8x4-pixel tiles of all
 // frames (tile index -> frame, tile row, tile column).
 // -------------------------------------------------------------------------
-template <bool SMEM, bool REPACK, bool COUNT>
+template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
 __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOCKS_SMALL) render_kernel(const __grid_constant__ RtParams P) {
     // dynamic shared memory: [hot scene (resident only)] [per-warp scratch] [per-warp tile buffers + barriers (streaming only)]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -841,8 +983,9 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
     size_t off4 = 0;                         // in float4 units
     if (SMEM) {
         // stage the hot scene once per CTA (persistent: once per SM-slot per launch)
-        const int nb4 = P.n_box * RT_BOX_F4, ns4 = P.n_sph;
-        for (int i = threadIdx.x; i < nb4; i += kThreads) smem_f4[i] = __ldg(P.box_hot + i);
+        const int nb4 = P.n_box * box_tile_f4<CULL>(), ns4 = P.n_sph;
+        const float4* __restrict__ box_src = CULL ? P.box_cull : P.box_hot;
+        for (int i = threadIdx.x; i < nb4; i += kThreads) smem_f4[i] = __ldg(box_src + i);
         for (int i = threadIdx.x; i < ns4; i += kThreads) smem_f4[nb4 + i] = __ldg(P.sph_hot + i);
         w.box_off4 = 0u;
         w.sph_off4 = (uint32_t)nb4;
@@ -881,6 +1024,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
 
     RtCounters cnt;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
+    cnt.cull_tests = cnt.warp_iters = 0ull;
 
     // Work distribution: the first round of tiles is static (tile = global warp id); after that
     // each warp pulls the next tile index from a global counter (zeroed by the host before the
@@ -900,7 +1044,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
             float jx, jy;
             jitter(P, px, py, s, jx, jy);
             const V3 dir = primary_dir(P, cam, px, py, jx, jy);
-            const V3 c = trace_sample<SMEM, REPACK, COUNT>(P, w, valid, org, dir, cnt);
+            const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid, org, dir, cnt);
             sum = sum + c;
         }
         const float fs = (float)P.spp;
@@ -929,9 +1073,11 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
 
     if (COUNT) {
         // warp-reduce then one atomic per warp per counter
-        unsigned long long v[8] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests, cnt.red_pixels, cnt.pad};
+        if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
+        unsigned long long v[10] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters};
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < 10; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);
@@ -943,7 +1089,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
 
 // Launchers with C linkage-free, namespace-qualified names; called from rt_host.cpp.
 namespace RT_NS {
-inline size_t hot_smem_bytes(const RtParams& P) { return ((size_t)P.n_box * RT_BOX_F4 + (size_t)P.n_sph) * sizeof(float4); }
+inline size_t hot_smem_bytes(const RtParams& P, bool cull) { return ((size_t)P.n_box * (cull ? 1 : RT_BOX_F4) + (size_t)P.n_sph) * sizeof(float4); }
 inline size_t scratch_smem_bytes() { return (size_t)kWarps * kScratchBytes; }
 inline size_t stream_smem_bytes() { return (size_t)kWarps * (2 * kTileBytes + 16); }
 size_t resident_limit_bytes(int max_smem_optin);

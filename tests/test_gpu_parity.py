@@ -174,6 +174,72 @@ def test_scaled_scene_streaming_pixel_subset(tracer, n):
     assert_parity(got, ref, "scaled n=%d subset" % n)
 
 
+@pytest.mark.parametrize("n,w,h,depth", [(200, 320, 180, 2), (1024, 480, 270, 1), (4096, 480, 270, 0),
+                                         (16384, 256, 144, 1)])
+def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
+    """Large scenes run the slab test (glsl:655-680) behind a conservative bounding-sphere test.
+    It may only skip tests that would have missed: the frame is BYTE-identical with it on or off,
+    as a whole frame and as 135-row-style unaligned bands; fewer slab tests are executed."""
+    sc, cam = rt.scaled_scene(n, max_depth=depth), rt.builtin_camera(0.0)
+    _, st_on = tracer.render(sc, cam, w, h, want_stats=True)
+    _, st_off = tracer.render(sc, cam, w, h, want_stats=True, no_cull=True)
+    on = tracer.render(sc, cam, w, h)                    # the shipped kernels (the counting twins are
+    off = tracer.render(sc, cam, w, h, no_cull=True)     # separate instantiations)
+    assert np.array_equal(on, off)
+    assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
+    assert st_off["cull_tests"] == 0 and st_on["cull_tests"] > 0
+    assert st_on["box_tests"] < st_off["box_tests"] // 4
+    canvas = np.empty_like(on)
+    edges = [0, 37, 90, h]
+    for y0, y1 in zip(edges[:-1], edges[1:]):
+        canvas[y0:y1] = tracer.render(sc, cam, w, h, y0=y0, y1=y1, band_only=True)
+    assert np.array_equal(canvas, on)
+
+
+def _far_scene(cube_half):
+    base = rt.builtin_scene(0.0, 1)
+    n = 64
+    objs = (rt.Object * n)()
+    rng = np.random.default_rng(7)
+    for i in range(n):
+        o = objs[i]
+        o.sphere_radius = -1.0
+        o.material = base.objects[1 + i % 4].material
+        far = 2000.0 if i % 3 == 0 else 8.0
+        ctr = rng.uniform(-1, 1, 3) * far
+        o.position[:] = [float(x) for x in ctr]
+        o.angles[:] = [float(x) for x in rng.uniform(0, 360, 3)]
+        if i % 7 == 6:
+            o.sphere_radius = float(rng.uniform(0.2, 300.0 if far > 100 else 2.0))
+        else:
+            hx = rng.uniform(0.001, 0.01, 3) if i % 5 == 0 else rng.uniform(0.2, 200.0 if far > 100 else 2.0, 3)
+            o.box_mins[:] = [float(-x) for x in hx]
+            o.box_maxs[:] = [float(x) for x in hx]
+    objs[0] = base.objects[0]                       # the enclosing cube: the camera is inside it
+    objs[0].box_mins[:] = [-cube_half] * 3
+    objs[0].box_maxs[:] = [cube_half] * 3
+    objs[1].box_mins[:] = [-1, -1, 0]
+    objs[1].box_maxs[:] = [1, 1, 0]                 # flat box: never hit (glsl:680)
+    return rt.SceneData(objs, base.lights, 2)
+
+
+def test_bounding_sphere_test_far_and_tiny_objects(tracer):
+    """Conservativeness away from the +-11 room: boxes and spheres 2000 units out (inside the
+    t < 10000 limit, glsl:740), boxes of millimetre size, a flat box, the camera inside a box.
+    With a +-3000 enclosing cube the shader's own FP32 quadratic (glsl:586-591: qb*qb - 4*qa*qc with
+    |dir| ~ 3000) is rounding noise for shadow rays, so only the op-for-op strict kernel can be held
+    to the oracle there; the fast kernel is held to it in the +-11 room."""
+    cam = rt.builtin_camera(0.0)
+    for half in (11.0, 3000.0):
+        sc = _far_scene(half)
+        on = tracer.render(sc, cam, 320, 180)
+        assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=True))
+        ref = ob.render(sc, cam, 320, 180)
+        _check(tracer.render(sc, cam, 320, 180, strict=True), ref, "far/tiny objects strict", need_edges=False)
+        if half < 100.0:
+            _check(on, ref, "far/tiny objects", need_edges=False)
+
+
 def test_edge_case_scenes(tracer):
     cam = rt.builtin_camera(0.0)
     # empty scene: every ray misses -> black, alpha 0 (semantics item 7)
