@@ -812,7 +812,7 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // -------------------------------------------------------------------------
 template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
 __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool valid, V3 org, V3 dir,
-                                           RtCounters& cnt) {
+                                           bool have_first, float first_t, int first_idx, RtCounters& cnt) {
     // pending rays: origin, direction, weight, remaining depth
     float stk[kStack][8];
     int sp = 0;
@@ -842,7 +842,12 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             best[0] = 0.0f;
         }
         // PHASE 0 (glsl:956-967)
-        trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, o[0], d[0], best[0], bidx[0], cnt);
+        if (have_first) {           // warp-uniform: the root ray was traced by the caller
+            if (act) { best[0] = first_t; bidx[0] = first_idx; }
+            have_first = false;
+        } else {
+            trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, o[0], d[0], best[0], bidx[0], cnt);
+        }
         const bool hit = act && bidx[0] >= 0;
         if (COUNT && act) { cnt.rays++; cnt.nodes++; cnt.hit_nodes += hit; }
         if (COUNT) cnt.warp_iters++;
@@ -1029,42 +1034,87 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
     // Work distribution: the first round of tiles is static (tile = global warp id); after that
     // each warp pulls the next tile index from a global counter (zeroed by the host before the
     // launch), so long and short tiles (glass vs wall, occluded vs open) even out.
+    // Large scenes: a work item is NP = 3 horizontally adjacent 8x4 tiles, one pixel of each per lane.
+    // The three primary rays of a lane start at the camera (glsl:391), so they go through the object
+    // loop together with the origin moved into each primitive's frame once (like the shadow rays of
+    // one hit point); P.tiles_x counts work items.
+    constexpr int NP = REPACK ? kShadowBatch : 1;
     for (long long tile = warp_global; tile < n_tiles;) {
         const int frame = (int)(tile / tiles_per_frame);
         const int tin = (int)(tile - (long long)frame * tiles_per_frame);
         const int ty = tin / P.tiles_x, tx = tin - ty * P.tiles_x;
-        const int px = tx * 8 + lx;
         const int py = P.y0 + ty * 4 + ly;
-        const bool valid = px < P.width && py < P.y1;
+        int px[NP]; bool valid[NP];
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            px[q] = (tx * NP + q) * 8 + lx;
+            valid[q] = px[q] < P.width && py < P.y1;
+        }
         const RtCameraDev* __restrict__ cam = P.cams + frame;
         const V3 org = mk(cam->position[0], cam->position[1], cam->position[2]);   // glsl:391
 
-        V3 sum = mk(0.0f, 0.0f, 0.0f);
+        V3 sum[NP];
+#pragma unroll
+        for (int q = 0; q < NP; ++q) sum[q] = mk(0.0f, 0.0f, 0.0f);
         for (int s = 0; s < P.spp; ++s) {
-            float jx, jy;
-            jitter(P, px, py, s, jx, jy);
-            const V3 dir = primary_dir(P, cam, px, py, jx, jy);
-            const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid, org, dir, cnt);
-            sum = sum + c;
+            V3 dir[kShadowBatch];
+#pragma unroll
+            for (int q = 0; q < NP; ++q) {
+                float jx, jy;
+                jitter(P, px[q], py, s, jx, jy);
+                dir[q] = primary_dir(P, cam, px[q], py, jx, jy);
+            }
+            if (NP == 1) {
+                sum[0] = sum[0] + trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid[0], org, dir[0], false, 0.0f, -1, cnt);
+            } else {
+                // PHASE 0 of the three root frames (glsl:956-967), shared origin
+                V3 o3[kShadowBatch];
+                float best[kShadowBatch]; int bidx[kShadowBatch];
+#pragma unroll
+                for (int q = 0; q < kShadowBatch; ++q) {
+                    o3[q] = org; bidx[q] = -1;
+                    best[q] = valid[q] ? kFar : 0.0f;
+                }
+                const int n_obj_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
+                tile_begin<SMEM, CULL>(P, w);
+                for (int t = 0; t < n_obj_tiles; ++t) {
+                    const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_obj_tiles);
+                    any_tile<kShadowBatch, false, true, COUNT, CULL>(P, recs, t, o3, dir, best, bidx, cnt);
+                }
+                // one copy of the bounce machinery in the instruction stream: rolled loop, selected operands
+#pragma unroll 1
+                for (int q = 0; q < NP; ++q) {
+                    const V3 dq = q == 0 ? dir[0] : (q == 1 ? dir[1] : dir[2]);
+                    const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
+                    const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
+                    const bool vq = q == 0 ? valid[0] : (q == 1 ? valid[1] : valid[2]);
+                    const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, cnt);
+                    if (q == 0) sum[0] = sum[0] + c;
+                    else if (q == 1) sum[1] = sum[1] + c;
+                    else sum[2] = sum[2] + c;
+                }
+            }
         }
-        const float fs = (float)P.spp;
-        const V3 fc = mk(fdiv(sum.x, fs), fdiv(sum.y, fs), fdiv(sum.z, fs));
-        // vec4(final_color, 0.0) -> RGBA8 (glsl:404): R | G<<8 | B<<16 | A(=0)<<24
-        const uint32_t word = unorm8(fc.x) | (unorm8(fc.y) << 8) | (unorm8(fc.z) << 16);
-
         uint8_t* frame_out = P.out + (long long)frame * P.frame_stride;
-        const long long pix = (long long)(py - P.out_row0) * P.width + px;
-        // 16-byte stores: lanes 4k..4k+3 hold 4 horizontally adjacent pixels
-        const uint32_t w1 = __shfl_down_sync(kFull, word, 1);
-        const uint32_t w2 = __shfl_down_sync(kFull, word, 2);
-        const uint32_t w3 = __shfl_down_sync(kFull, word, 3);
-        const bool vec_ok = ((P.width & 3) == 0) && (tx * 8 + 8 <= P.width) &&
-                            ((reinterpret_cast<uintptr_t>(frame_out) & 15) == 0);
-        if (vec_ok) {
-            if ((lane & 3) == 0 && py < P.y1)
-                *reinterpret_cast<uint4*>(frame_out + pix * 4) = make_uint4(word, w1, w2, w3);
-        } else if (valid) {
-            *reinterpret_cast<uint32_t*>(frame_out + pix * 4) = word;
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const float fs = (float)P.spp;
+            const V3 fc = mk(fdiv(sum[q].x, fs), fdiv(sum[q].y, fs), fdiv(sum[q].z, fs));
+            // vec4(final_color, 0.0) -> RGBA8 (glsl:404): R | G<<8 | B<<16 | A(=0)<<24
+            const uint32_t word = unorm8(fc.x) | (unorm8(fc.y) << 8) | (unorm8(fc.z) << 16);
+            const long long pix = (long long)(py - P.out_row0) * P.width + px[q];
+            // 16-byte stores: lanes 4k..4k+3 hold 4 horizontally adjacent pixels
+            const uint32_t w1 = __shfl_down_sync(kFull, word, 1);
+            const uint32_t w2 = __shfl_down_sync(kFull, word, 2);
+            const uint32_t w3 = __shfl_down_sync(kFull, word, 3);
+            const bool vec_ok = ((P.width & 3) == 0) && ((tx * NP + q) * 8 + 8 <= P.width) &&
+                                ((reinterpret_cast<uintptr_t>(frame_out) & 15) == 0);
+            if (vec_ok) {
+                if ((lane & 3) == 0 && py < P.y1)
+                    *reinterpret_cast<uint4*>(frame_out + pix * 4) = make_uint4(word, w1, w2, w3);
+            } else if (valid[q]) {
+                *reinterpret_cast<uint32_t*>(frame_out + pix * 4) = word;
+            }
         }
         unsigned long long next = 0ull;
         if (lane == 0) next = atomicAdd(P.tile_counter, 1ull);
