@@ -50,7 +50,11 @@ WORKLOADS = {
     "scaled_4k_1080p_d0": ("scaled", 4096, 1920, 1080, 1, 0),
     "scaled_16k_1080p_d0": ("scaled", 16384, 1920, 1080, 1, 0),
     "scaled_64k_1080p_d0": ("scaled", 65536, 1920, 1080, 1, 0),
+    "scaled_1k_1080p_d2": ("scaled", 1024, 1920, 1080, 1, 2),
+    # BASELINE config 5: 256 turntable poses at 1024x1024, whole frames sharded over the ranks
+    "batch256_1024_d4": ("batch", 5, 1024, 1024, 1, 4),
 }
+BATCH_FRAMES = 256
 DEFAULT_WORKLOAD = "builtin_1080p_d4"
 METRIC = "Mrays/s (rays x bounces), built-in scene 1080p"
 UNIT = "Mrays/s"
@@ -59,15 +63,22 @@ UNIT = "Mrays/s"
 # ray-dependent work only): box slab test 59, sphere test 41, closest-hit resolve 45, one shaded
 # light 95, primary-ray generation 76.
 F_BOX, F_SPH, F_HIT, F_LIGHT, F_PRIMARY = 59.0, 41.0, 45.0, 95.0, 76.0
+# Large scenes run the slab test behind a bounding-sphere test and the sphere roots behind the
+# discriminant: one such test is oc 3 + |oc|^2-r^2 6 (shared by the rays of one origin)
+# + d.oc 5 + discriminant 3 + compare 1, counted as 12 per ray; a sphere test that goes on to its roots
+# then costs the remaining 41 - 17 = 24.
+F_CULL, F_SPH_ROOTS = 12.0, 24.0
 
 
 def algorithmic_flops(st, samples):
-    return (F_BOX * st["box_tests"] + F_SPH * st["sphere_tests"] + F_HIT * st["hit_nodes"] +
-            F_LIGHT * st["shadow_rays"] + F_PRIMARY * samples)
+    """Flops of the tests actually EXECUTED (skipped tests are never credited)."""
+    f_sph = F_SPH_ROOTS if st["cull_tests"] else F_SPH
+    return (F_BOX * st["box_tests"] + f_sph * st["sphere_tests"] + F_CULL * st["cull_tests"] +
+            F_HIT * st["hit_nodes"] + F_LIGHT * st["shadow_rays"] + F_PRIMARY * samples)
 
 
 def make_scene(mod, kind, n, depth):
-    if kind == "builtin":
+    if kind in ("builtin", "batch"):
         return mod.builtin_scene(0.0, depth)
     sc = mod.scaled_scene(n)
     sc.max_depth = depth
@@ -143,7 +154,7 @@ def strided_pixels(width, height, n_pixels, seed=1):
 def cpu_time_sample(ob, wl, target_seconds, as_written=True):
     """Time the oracle on a pixel sample sized for about target_seconds; returns (Mrays/s, description, cores)."""
     kind, n, w, h, spp, depth = wl
-    scene = make_scene(ob, kind, n, depth) if kind == "builtin" else None
+    scene = make_scene(ob, kind, n, depth) if kind in ("builtin", "batch") else None
     if scene is None:
         import openglraytracer_b200 as rt   # scene GENERATOR only (host data); nothing is rendered by the product here
         scene = make_scene(rt, kind, n, depth)
@@ -204,7 +215,8 @@ def run_gpu(args, wl_name, wl):
     import torch
     import torch.distributed as dist
     import openglraytracer_b200 as rt
-    from openglraytracer_b200.multigpu import BandRenderer, gather_bands
+    from openglraytracer_b200.multigpu import (BandRenderer, PeerFrame, balanced_row_bands, frame_block,
+                                                 probe_row_cost, row_band)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -220,22 +232,30 @@ def run_gpu(args, wl_name, wl):
     kind, n_obj, w, h, spp, depth = wl
     scene = make_scene(rt, kind, n_obj, depth)
     cam = rt.builtin_camera(0.0)
+    batch = kind == "batch"
+    nfr = 1
+    cams = cam
+    if batch:   # whole frames per rank: poses [k0, k1) of the 256-pose turntable (glsl:343-358 orbit)
+        k0, k1 = frame_block(rank, world, BATCH_FRAMES)
+        poses = rt.turntable_cameras(BATCH_FRAMES)
+        nfr = k1 - k0
+        cams = (rt.Camera * nfr)(*[poses[k] for k in range(k0, k1)])
     tracer = rt.Raytracer(local)
     # a real (non-NULL) stream: the C ABI treats a NULL stream as "the context's own stream"
     stream = torch.cuda.Stream(dev)
     torch.cuda.set_stream(stream)
-    frame_dev = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
+    frame_dev = torch.empty((nfr, h, w, 4), dtype=torch.uint8, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
 
     # counters from the instrumented twin (untimed); the timed kernel is the plain one
     tracer.upload_scene(scene)
-    _, st = tracer.render(None, cam, w, h, spp=spp, out_device_ptr=frame_dev.data_ptr(), want_stats=True)
-    rays_per_frame = int(st["rays"])
-    flops_per_frame = algorithmic_flops(st, w * h * spp)
+    _, st = tracer.render(None, cams, w, h, spp=spp, out_device_ptr=frame_dev.data_ptr(), want_stats=True)
+    rays_per_frame = int(st["rays"])            # per launch of this rank (nfr frames in batch mode)
+    flops_per_frame = algorithmic_flops(st, nfr * w * h * spp)
     peak_tf, _ = rt.fp32_peak_tflops(local, 8192)
 
     def step():
-        tracer.render(None, cam, w, h, spp=spp, out_device_ptr=frame_dev.data_ptr(), async_=True,
+        tracer.render(None, cams, w, h, spp=spp, out_device_ptr=frame_dev.data_ptr(), async_=True,
                       stream=stream.cuda_stream)
 
     def barrier():
@@ -268,31 +288,39 @@ def run_gpu(args, wl_name, wl):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
     ms_per_step = total_ms / args.steps
-    value = world * rays_per_frame / (ms_per_step * 1e-3) / 1e6
+    rays_job = world * rays_per_frame           # frame mode: every rank renders its own copy of the frame (weak)
+    if batch and world > 1:                     # batch mode: the 256 poses are split over the ranks (strong)
+        t = torch.tensor([rays_per_frame], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        rays_job = int(t.item())
+    value = rays_job / (ms_per_step * 1e-3) / 1e6
 
     # e2e: the public call with host structs and a pinned host framebuffer
-    pin = rt.PinnedImage((h, w, 4))
-    scene_bytes = 132 * scene.objects_count + 60 * scene.scene.lights_count + 40
+    pin = rt.PinnedImage((nfr, h, w, 4) if batch else (h, w, 4))
+    scene_bytes = 132 * scene.objects_count + 60 * scene.scene.lights_count + 40 * nfr
     for _ in range(3):
-        tracer.render(scene, cam, w, h, spp=spp, out=pin.array)
+        tracer.render(scene, cams, w, h, spp=spp, out=pin.array)
     barrier()
     e2e_steps = max(3, min(args.steps, 50))
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        tracer.render(scene, cam, w, h, spp=spp, out=pin.array)
+        tracer.render(scene, cams, w, h, spp=spp, out=pin.array)
     barrier()
     e2e_s = time.perf_counter() - t0
     if world > 1:
         t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e_value = world * rays_per_frame * e2e_steps / e2e_s / 1e6
-    checksum = int(pin.array[::97, ::89].astype(np.uint64).sum())
+    e2e_value = rays_job * e2e_steps / e2e_s / 1e6
+    checksum = int(pin.array[..., ::97, ::89, :].astype(np.uint64).sum())
 
     # frame mode at N > 1: one frame split into contiguous row bands, NCCL gather on rank 0
     bands = None
-    if world > 1:
-        br = BandRenderer(tracer, w, h, rank, world, dev)
+    if world > 1 and not batch:
+        # contiguous row bands of equal COST (per-row ray counts from a 72-strip probe, same on every rank)
+        cost_bands = balanced_row_bands(probe_row_cost(tracer, None, cam, w, h), world)
+        torch.cuda.synchronize(dev)
+        br = BandRenderer(tracer, w, h, rank, world, dev, bands=cost_bands)
         for _ in range(3):
             br.render_and_gather(None, cam, spp=spp)
         barrier()
@@ -311,7 +339,33 @@ def run_gpu(args, wl_name, wl):
             same = bool(np.array_equal(full.cpu().numpy(), pin.array))
         bands = {"ms_per_frame": ms_b, "value": rays_per_frame / (ms_b * 1e-3) / 1e6, "unit": UNIT,
                  "scaling": "strong", "collective": "nccl gather of %d row bands to rank 0" % world,
+                 "bands": "contiguous, cost-balanced: " + str(cost_bands),
                  "byte_identical_to_single_gpu": same}
+        # fused gather: every rank's kernel stores its band straight into rank 0's frame (CUDA IPC, NVLink)
+        try:
+            for label, bset in (("peer_store", cost_bands),
+                                ("peer_store_equal_height_bands", [row_band(r, world, h) for r in range(world)])):
+                pf = PeerFrame(tracer, w, h, rank, world, dev, bands=bset)
+                for _ in range(3):
+                    pf.render(None, cam, spp=spp)
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(n_b):
+                    full = pf.render(None, cam, spp=spp)
+                e1.record(stream)
+                barrier()
+                t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms_p = float(t.item()) / n_b
+                same_p = bool(np.array_equal(full.cpu().numpy(), pin.array)) if rank == 0 else True
+                pf.close()
+                bands[label] = {"ms_per_frame": ms_p, "value": rays_per_frame / (ms_p * 1e-3) / 1e6,
+                                "collective": "none on the data path: kernels store into rank 0's frame over "
+                                              "NVLink (CUDA IPC mapping), one 4-byte all-reduce as completion flag",
+                                "byte_identical_to_single_gpu": same_p}
+        except Exception as exc:   # IPC refused (container policy): the NCCL gather above stands
+            bands["peer_store"] = {"unavailable": repr(exc)[:200]}
 
     clocks = sampler.stop(t_region0, t_region1) if rank == 0 else None
     if rank == 0:
@@ -320,17 +374,17 @@ def run_gpu(args, wl_name, wl):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong" if batch else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl_name, "scene": kind, "objects": n_obj, "width": w, "height": h, "spp": spp,
-                       "max_depth": depth, "rays_per_frame": rays_per_frame,
-                       "rays_traversed_per_frame": rays_per_frame - int(st["rays_not_traversed"]),
+                       "max_depth": depth, "rays_per_frame": rays_per_frame // nfr,
+                       "rays_traversed_per_frame": (rays_per_frame - int(st["rays_not_traversed"])) // nfr,
                        "ray_unit": "one get_closest_collision call of the reference (glsl:738); shadow rays whose outcome "
                                    "cannot change the pixel are counted but not traversed",
-                       "frames_per_step": world,
+                       "frames_per_step": BATCH_FRAMES if batch else world,
                        "parallelism": "frames sharded over %d GPU(s), no data-path collective" % world,
                        "l2": "flushed between timed steps (256 MiB write)", "kernel": "fast (fmad on, no fast-math)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": scene_bytes,
-                    "d2h_bytes_per_step": w * h * 4, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
+                    "d2h_bytes_per_step": nfr * w * h * 4, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "checksum": checksum},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
@@ -338,7 +392,12 @@ def run_gpu(args, wl_name, wl):
                          "peak_source": "FP32 FMA-chain microbenchmark in this run (MEASURED_PEAKS.json has no FP32 "
                                         "figure); nominal 148 SM x 128 x 2 x 1.965 GHz = 74.4",
                          "algorithmic_flops_per_launch": flops_per_frame, "kernel_ms": kernel_ms,
-                         "box_tests": int(st["box_tests"]), "sphere_tests": int(st["sphere_tests"])},
+                         "box_tests": int(st["box_tests"]), "sphere_tests": int(st["sphere_tests"]),
+                         "bounding_sphere_tests": int(st["cull_tests"]),
+                         "lane_use": st["nodes"] / max(1, 32 * st["warp_iters"]),
+                         "flops_per_unit": "slab test 59, sphere 41 (24 after its discriminant), bounding-sphere / "
+                                           "discriminant test 12, hit resolve 45, shaded light 95, primary ray 76; "
+                                           "executed tests only"},
             "clocks": clocks,
         }
         if bands:

@@ -202,6 +202,12 @@ int rt_write_raw(const char* path, const uint8_t* rgba, int width, int height);
  * TFLOP/s (2 flop per FMA).  Denominator check for the FP32 roofline. */
 int rt_fp32_peak_tflops(int device, int iters, double* tflops, float* ms);
 
+/* Plain device memory on the current device (cudaMalloc / cudaFree): a framebuffer whose
+ * CUDA IPC handle maps exactly onto the pointer (a pointer carved out of a caching allocator's
+ * block would export the block). */
+int rt_device_alloc(void** device_ptr, size_t bytes);
+int rt_device_free(void* device_ptr);
+
 /* Multi-GPU helper for the fused gather: export/import a CUDA IPC handle of a
  * device framebuffer so that other ranks' kernels store their row band directly
  * into rank 0's buffer over NVLink. handle is 64 bytes. */

@@ -71,7 +71,7 @@ EXPORTS = [
     "rt_synchronize", "rt_options_default", "rt_host_alloc", "rt_host_free", "rt_render", "rt_render_ex",
     "rt_render_batch", "rt_upload_scene", "rt_render_uploaded", "rt_builtin_scene", "rt_builtin_camera",
     "rt_orbit_camera", "rt_scaled_scene", "rt_write_ppm", "rt_write_raw", "rt_fp32_peak_tflops",
-    "rt_ipc_export", "rt_ipc_import", "rt_ipc_close",
+    "rt_ipc_export", "rt_ipc_import", "rt_ipc_close", "rt_device_alloc", "rt_device_free",
 ]
 
 _lib = None
@@ -114,6 +114,8 @@ def lib():
     L.rt_ipc_export.argtypes = [vp, C.c_char_p]
     L.rt_ipc_import.argtypes = [C.c_char_p, C.POINTER(vp)]
     L.rt_ipc_close.argtypes = [vp]
+    L.rt_device_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+    L.rt_device_free.argtypes = [vp]
     for name in EXPORTS:
         fn = getattr(L, name)
         if name not in ("rt_last_error_string", "rt_kernel_launch_count", "rt_options_default"):

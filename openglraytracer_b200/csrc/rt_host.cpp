@@ -496,6 +496,16 @@ int rt_render(const rt_scene* scene, const rt_camera* camera, uint8_t* out_rgba,
     return rt_render_ex(ctxs[dev], scene, camera, out_rgba, width, height, nullptr);
 }
 
+int rt_device_alloc(void** device_ptr, size_t bytes) {
+    if (!device_ptr || bytes == 0) return fail(RT_ERR_BAD_ARG, "bad rt_device_alloc arguments");
+    CU(cudaMalloc(device_ptr, bytes));
+    return RT_OK;
+}
+int rt_device_free(void* device_ptr) {
+    if (device_ptr) CU(cudaFree(device_ptr));
+    return RT_OK;
+}
+
 int rt_ipc_export(void* device_ptr, uint8_t handle64[64]) {
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     if (!device_ptr || !handle64) return fail(RT_ERR_BAD_ARG, "bad rt_ipc_export arguments");

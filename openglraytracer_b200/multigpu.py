@@ -22,17 +22,66 @@ def frame_block(rank, world, n_frames):
     return (rank * n_frames) // world, ((rank + 1) * n_frames) // world
 
 
-def gather_bands(band, height, width, group=None, dst=0):
+def balanced_row_bands(row_cost, world, align=4):
+    """Contiguous bands of (nearly) equal COST: row_cost[y] is any per-row cost estimate (rays,
+    time ...).  Boundaries are multiples of `align` rows (the kernel's tiles are 4 rows high), every
+    band keeps at least one row, and the bands partition [0, H).  Deterministic: every rank that
+    feeds the same costs gets the same bands, so no exchange is needed.  Floor and glass rows cost
+    more rays than wall rows (SURVEY §7 hard part 5); equal-height bands leave GPUs idle."""
+    h = len(row_cost)
+    if world >= h:
+        return [row_band(r, world, h) for r in range(world)]
+    total = float(sum(row_cost))
+    if total <= 0.0:
+        return [row_band(r, world, h) for r in range(world)]
+    cuts = [0]
+    acc, y = 0.0, 0
+    for r in range(1, world):
+        target = total * r / world
+        while y < h and acc + row_cost[y] * 0.5 < target:
+            acc += row_cost[y]
+            y += 1
+        c = int(round(y / align)) * align
+        c = max(c, cuts[-1] + 1)
+        c = min(c, h - (world - r))
+        cuts.append(c)
+    cuts.append(h)
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def probe_row_cost(raytracer, scene, camera, width, height, spp=1, strips=72, shrink=8):
+    """Per-row cost estimate for balanced_row_bands: the reference ray count (rt_stats.rays) of
+    `strips` horizontal strips rendered at 1/shrink of the width with the counting kernel (a few
+    tiny launches; the counts are deterministic, so every rank computes the same numbers)."""
+    import numpy as np
+    strips = max(1, min(strips, height))
+    w_probe = max(8, width // shrink)
+    cost = np.zeros(height, np.float64)
+    if scene is not None:
+        raytracer.upload_scene(scene)
+    for s in range(strips):
+        y0, y1 = (s * height) // strips, ((s + 1) * height) // strips
+        # one row in the middle of the strip stands for the strip; absolute pixel rows keep the geometry
+        ym = (y0 + y1) // 2
+        _, st = raytracer.render(None, camera, w_probe, height, spp=1, y0=ym, y1=ym + 1, band_only=True,
+                                 want_stats=True)
+        cost[y0:y1] = st["rays"] + 0.25 * st["cull_tests"] / max(1, w_probe)
+    return cost
+
+
+def gather_bands(band, height, width, group=None, dst=0, bands=None):
     """Gather every rank's band (uint8 [rows_r, W, 4]) into the full frame on `dst`.
 
-    Bands may differ by one row when H % G != 0; they are padded to the largest
-    band for the collective and trimmed on arrival.  Returns uint8 [H, W, 4] on
-    dst, None elsewhere.
+    Bands may differ in height (H % G != 0, or cost-balanced bands); they are padded to the
+    largest band for the collective and trimmed on arrival.  Returns uint8 [H, W, 4] on dst, None
+    elsewhere.
     """
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
-    max_rows = max(row_band(r, world, height)[1] - row_band(r, world, height)[0] for r in range(world))
-    y0, y1 = row_band(rank, world, height)
+    if bands is None:
+        bands = [row_band(r, world, height) for r in range(world)]
+    max_rows = max(b - a for a, b in bands)
+    y0, y1 = bands[rank]
     assert band.shape == (y1 - y0, width, 4) and band.dtype == torch.uint8, (band.shape, band.dtype)
     if y1 - y0 == max_rows:
         send = band.contiguous()
@@ -44,7 +93,7 @@ def gather_bands(band, height, width, group=None, dst=0):
         dist.gather(send, parts, dst=dst, group=group)
         frame = torch.empty((height, width, 4), dtype=torch.uint8, device=band.device)
         for r in range(world):
-            a, b = row_band(r, world, height)
+            a, b = bands[r]
             frame[a:b] = parts[r][: b - a]
         return frame
     dist.gather(send, None, dst=dst, group=group)
@@ -55,11 +104,12 @@ class BandRenderer:
     """Row-band renderer of one rank: renders rows [y0, y1) of every frame into a
     device tensor through the C ABI (device output, caller's stream)."""
 
-    def __init__(self, raytracer, width, height, rank, world, device):
+    def __init__(self, raytracer, width, height, rank, world, device, bands=None):
         self.rt = raytracer
         self.width, self.height = width, height
         self.rank, self.world = rank, world
-        self.y0, self.y1 = row_band(rank, world, height)
+        self.bands = bands if bands is not None else [row_band(r, world, height) for r in range(world)]
+        self.y0, self.y1 = self.bands[rank]
         self.band = torch.empty((self.y1 - self.y0, width, 4), dtype=torch.uint8, device=device)
         # A real stream handle: the C ABI reads a NULL stream as "the context's own stream",
         # and torch's legacy default stream IS the NULL handle.
@@ -77,6 +127,93 @@ class BandRenderer:
     def render_and_gather(self, scene, camera, group=None, **kw):
         band = self.render(scene, camera, **kw)
         with torch.cuda.stream(self.stream):
-            frame = gather_bands(band, self.height, self.width, group=group)
+            frame = gather_bands(band, self.height, self.width, group=group, bands=self.bands)
         torch.cuda.current_stream(self.band.device).wait_stream(self.stream)
         return frame
+
+
+class _RawCudaBuffer:
+    """A cudaMalloc'ed buffer exposed through __cuda_array_interface__ so that torch can view it."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class PeerFrame:
+    """Fused gather (SURVEY §5 / §8e stage 2): rank `dst` owns the frame; every other rank maps
+    it through a CUDA IPC handle and its render kernel's 16-byte framebuffer stores
+    (rt_kernel.cuh, glsl:404 imageStore) land directly in that buffer over NVLink.  The only
+    collective left is a one-element all-reduce that tells `dst` every band is complete."""
+
+    def __init__(self, raytracer, width, height, rank, world, device, group=None, dst=0, bands=None):
+        import ctypes as C
+        from . import _abi
+        self.rt, self.width, self.height = raytracer, width, height
+        self.rank, self.world, self.dst, self.group = rank, world, dst, group
+        self.y0, self.y1 = (bands if bands is not None else [row_band(r, world, height) for r in range(world)])[rank]
+        self.device = device
+        self.stream = torch.cuda.Stream(device)
+        self._lib = _abi.lib()
+        nbytes = width * height * 4
+        handle = torch.zeros(64, dtype=torch.uint8, device=device)
+        self._own = C.c_void_p()
+        self._mapped = C.c_void_p()
+        # Every rank goes through the same collectives whatever fails locally; the outcome is agreed
+        # with an all-reduce so that either all ranks own a working PeerFrame or all raise.
+        err = None
+        self.ptr = None
+        if rank == dst:
+            try:
+                _abi.check(self._lib.rt_device_alloc(C.byref(self._own), nbytes), "rt_device_alloc")
+                buf = C.create_string_buffer(64)
+                _abi.check(self._lib.rt_ipc_export(self._own, buf), "rt_ipc_export")
+                handle.copy_(torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8))
+                self.ptr = self._own.value
+            except Exception as exc:
+                err = exc
+        dist.broadcast(handle, src=dst, group=group)
+        if rank != dst:
+            try:
+                raw = bytes(handle.cpu().numpy().tobytes())
+                _abi.check(self._lib.rt_ipc_import(raw, C.byref(self._mapped)), "rt_ipc_import")
+                self.ptr = self._mapped.value
+            except Exception as exc:
+                err = exc
+        ok = torch.tensor([0 if err else 1], dtype=torch.int32, device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok.item()) == 0:
+            if self._mapped:
+                self._lib.rt_ipc_close(self._mapped)
+            if self._own:
+                self._lib.rt_device_free(self._own)
+            raise RuntimeError("PeerFrame: CUDA IPC mapping of rank %d's frame failed on some rank (%r)" % (dst, err))
+        self.frame = None
+        if rank == dst:
+            self.frame = torch.as_tensor(_RawCudaBuffer(self.ptr, (height, width, 4)), device=device)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def render(self, scene, camera, **kw):
+        """All ranks: render this rank's band into dst's frame, then the completion all-reduce.
+        Returns the full frame (uint8 [H, W, 4]) on dst, None elsewhere; ordered on the caller's
+        current stream."""
+        cur = torch.cuda.current_stream(self.device)
+        self.stream.wait_stream(cur)
+        self.rt.render(scene, camera, self.width, self.height, y0=self.y0, y1=self.y1, band_only=False,
+                       out_device_ptr=self.ptr, async_=True, stream=self.stream.cuda_stream, **kw)
+        with torch.cuda.stream(self.stream):
+            dist.all_reduce(self._flag, group=self.group)
+        cur.wait_stream(self.stream)
+        return self.frame
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+        if self._mapped:
+            self._lib.rt_ipc_close(self._mapped)
+            self._mapped = None
+        dist.barrier(group=self.group)
+        if self._own:
+            self.frame = None
+            self._lib.rt_device_free(self._own)
+            self._own = None

@@ -62,3 +62,46 @@ def test_band_gather_is_byte_identical_to_single_rank(tmp_path, world, h):
     mp.spawn(_worker, args=(world, _free_port(), w, h, out), nprocs=world, join=True)
     ref = ob.render(ob.builtin_scene(0.7, 2), ob.builtin_camera(0.7), w, h)
     assert np.array_equal(np.load(out), ref)
+
+
+def test_cost_balanced_bands_partition_and_balance():
+    from openglraytracer_b200.multigpu import balanced_row_bands
+    rng = np.random.default_rng(3)
+    for h in (8, 45, 270, 1080, 2160):
+        cost = rng.uniform(0.5, 1.5, h)
+        cost[: h // 3] *= 4.0                       # floor / glass rows cost more rays than wall rows
+        for g in (1, 2, 3, 4, 8):
+            bands = balanced_row_bands(cost, g)
+            assert bands[0][0] == 0 and bands[-1][1] == h and len(bands) == g
+            assert all(bands[i][1] == bands[i + 1][0] for i in range(g - 1))
+            assert all(b > a for a, b in bands)
+            if h >= 270:
+                per = [cost[a:b].sum() for a, b in bands]
+                assert max(per) <= 1.08 * (cost.sum() / g) + 4 * cost.max()
+                assert all(a % 4 == 0 for a, _ in bands)
+    assert balanced_row_bands(np.zeros(16), 4) == [(0, 4), (4, 8), (8, 12), (12, 16)]
+
+
+def _worker_uneven(rank, world, port, w, h, bands, out_path):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import oracle_binding as ob
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sc, cam = ob.builtin_scene(0.2, 1), ob.builtin_camera(0.2)
+    y0, y1 = bands[rank]
+    canvas = ob.render(sc, cam, w, h, y0=y0, y1=y1, threads=2)
+    frame = gather_bands(torch.from_numpy(np.ascontiguousarray(canvas[y0:y1])), h, w, bands=bands)
+    if rank == 0:
+        np.save(out_path, frame.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_uneven_band_gather_is_byte_identical(tmp_path):
+    import oracle_binding as ob
+    w, h, bands = 64, 40, [(0, 8), (8, 40)]
+    out = str(tmp_path / "frame.npy")
+    mp.spawn(_worker_uneven, args=(2, _free_port(), w, h, bands, out), nprocs=2, join=True)
+    assert np.array_equal(np.load(out), ob.render(ob.builtin_scene(0.2, 1), ob.builtin_camera(0.2), w, h))
