@@ -193,6 +193,18 @@ int rt_orbit_camera(float speed, rt_camera* camera);
  * rt_object, lights 3 rt_light. */
 int rt_scaled_scene(int n_objects, uint64_t seed, rt_object* objects, rt_light* lights3, rt_scene* scene);
 
+/* Scene / camera description on the wire: the data the shader hard-codes in its globals
+ * (glsl:22, 74-157, 199-224, 261-321, 334-364) as a line-oriented text file, fields in the order
+ * of the structs above, 9 significant digits (every FP32 bit pattern survives save -> load).
+ * Format in openglraytracer_b200/csrc/rt_scene_io.cpp.  camera may be NULL on save; a file
+ * without a camera record loads with rt_scene_file_camera() == NULL. */
+typedef struct rt_scene_file rt_scene_file;
+int rt_scene_save(const char* path, const rt_scene* scene, const rt_camera* camera);
+int rt_scene_load(const char* path, rt_scene_file** out);
+const rt_scene* rt_scene_file_scene(const rt_scene_file* sf);
+const rt_camera* rt_scene_file_camera(const rt_scene_file* sf);
+void rt_scene_file_free(rt_scene_file* sf);
+
 /* Replaces the draw_screen_vert/frag blit (main.cpp:240-260): binary PPM (P6),
  * rows flipped so the picture is upright, alpha dropped (frag:9). */
 int rt_write_ppm(const char* path, const uint8_t* rgba, int width, int height);

@@ -13,6 +13,7 @@ Everything goes through the C ABI (include/rt_b200.h); numpy only holds the
 host pixels.  No CPU fallback exists.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -221,3 +222,38 @@ def fp32_peak_tflops(device=-1, iters=4096):
 
 def kernel_launch_count():
     return int(_abi.lib().rt_kernel_launch_count())
+
+
+def save_scene(path, scene, camera=None):
+    """Write the scene (and optionally the camera uniforms) as an `rtscene 1` text file:
+    the shader's hard-coded globals (glsl:22, 199-224, 261-321, 334-364) on the wire."""
+    sc = scene.scene if isinstance(scene, SceneData) else scene
+    cam = C.byref(camera) if camera is not None else None
+    check(_abi.lib().rt_scene_save(os.fsencode(path), C.byref(sc), cam), "rt_scene_save")
+
+
+def load_scene(path):
+    """Read an `rtscene 1` file: returns (SceneData, Camera or None).  The arrays are copied
+    out of the loader's storage, so the result owns its memory."""
+    L = _abi.lib()
+    h = C.c_void_p()
+    check(L.rt_scene_load(os.fsencode(path), C.byref(h)), "rt_scene_load")
+    try:
+        sc = L.rt_scene_file_scene(h).contents
+        objs = (Object * max(1, sc.objects_count))()
+        lights = (Light * max(1, sc.lights_count))()
+        for i in range(sc.objects_count):
+            C.memmove(C.byref(objs[i]), C.byref(sc.objects[i]), C.sizeof(Object))
+        for j in range(sc.lights_count):
+            C.memmove(C.byref(lights[j]), C.byref(sc.lights[j]), C.sizeof(Light))
+        data = SceneData(objs, lights, sc.max_depth)
+        data.scene.objects_count = sc.objects_count
+        data.scene.lights_count = sc.lights_count
+        cp = L.rt_scene_file_camera(h)
+        cam = None
+        if cp:
+            cam = Camera()
+            C.memmove(C.byref(cam), cp, C.sizeof(Camera))
+        return data, cam
+    finally:
+        L.rt_scene_file_free(h)

@@ -240,6 +240,8 @@ int validate_scene(const rt_scene* scene) {
 extern "C" {
 
 int rt_abi_version(void) { return RT_ABI_VERSION; }
+/* shared error sink for the other translation units of the library (rt_scene_io.cpp); not in the header */
+int rt_set_error_(int code, const char* msg) { return fail(code, "%s", msg ? msg : ""); }
 const char* rt_last_error_string(void) { return g_err; }
 uint64_t rt_kernel_launch_count(void) { return g_launches.load(); }
 

@@ -26,7 +26,7 @@ def _has_gpu():
 
 def test_header_symbols_all_exported():
     hdr = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
-    declared = set(re.findall(r"^\s*(?:int|void|uint64_t|const char\*)\s+(rt_[a-z0-9_]+)\s*\(", hdr, re.M))
+    declared = set(re.findall(r"^\s*(?:int|void|uint64_t|const char\*|const rt_scene\*|const rt_camera\*)\s+(rt_[a-z0-9_]+)\s*\(", hdr, re.M))
     assert declared, "no declarations parsed"
     assert declared == set(_abi.EXPORTS), declared ^ set(_abi.EXPORTS)
     L = _abi.lib()
