@@ -129,7 +129,8 @@ typedef struct rt_options {
     int32_t async;            /* 1 = do not synchronise (device output only); pair with rt_synchronize() */
     void* stream;             /* cudaStream_t to launch on; NULL = the context's own stream */
     rt_stats* stats;          /* optional counters/timings */
-    int32_t no_cull;          /* 1 = large scenes run every slab test (no bounding-sphere test first); same image */
+    int32_t no_cull;          /* A/B switches, same image: bit 0 = large scenes run every slab test (no bounding-sphere
+                               * test first); bit 1 = shadow rays do not use the per-light records */
 } rt_options;
 
 typedef struct rt_context rt_context;

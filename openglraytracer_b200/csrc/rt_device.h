@@ -73,6 +73,7 @@ struct RtParams {
     const float4* box_hot;
     const float4* box_cull;     /* per box: (world-space centre, padded squared circumradius) */
     const float4* sph_hot;      /* (cx, cy, cz, r*r) */
+    const float4* obj_lrec;     /* per 64-object tile, per lit light: (L - centre, |L - centre|^2 - R'^2), boxes then spheres */
     const int32_t* box_obj;     /* hot index -> original object index */
     const int32_t* sph_obj;
     const RtCold* cold;
@@ -89,6 +90,7 @@ struct RtParams {
     uint32_t seed;
     int32_t tiles_x, tiles_y;   /* 8x4-pixel warp tiles covering width x (y1-y0) */
     int32_t resident;           /* 1: whole hot scene staged in shared memory once per CTA */
+    int32_t n_lit;              /* lit lights with per-light records (1..3), 0 = shadow rays take the generic path */
     int32_t cull;               /* 1: large-scene kernels run the slab test behind the bounding-sphere test */
 };
 

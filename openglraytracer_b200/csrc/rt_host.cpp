@@ -13,7 +13,9 @@
  */
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -86,6 +88,8 @@ struct DevBuf {
 struct HostScene {
     std::vector<float> box_fast, box_strict;   // float4 records
     std::vector<float> box_cull;               // (world-space centre, padded squared circumradius) per box
+    std::vector<float> obj_lrec;               // per 64-object tile x lit light: (L - c, |L - c|^2 - R'^2)
+    int n_lit = 0;                             // lit lights with records (0: more than 3, or none)
     std::vector<float> sph;                    // (c, r*r)
     std::vector<int32_t> box_obj, sph_obj;
     std::vector<RtCold> cold;
@@ -101,7 +105,7 @@ struct rt_context {
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    DevBuf<float> d_box_fast, d_box_strict, d_box_cull, d_sph;
+    DevBuf<float> d_box_fast, d_box_strict, d_box_cull, d_obj_lrec, d_sph;
     DevBuf<int32_t> d_box_obj, d_sph_obj;
     DevBuf<RtCold> d_cold;
     DevBuf<RtLightDev> d_lights;
@@ -113,7 +117,7 @@ struct rt_context {
     size_t h_pinned_cap = 0;
     // uploaded scene
     bool have_scene = false;
-    int n_box = 0, n_sph = 0, n_lights = 0, max_depth = 0;
+    int n_box = 0, n_sph = 0, n_lights = 0, max_depth = 0, n_lit = 0;
 };
 
 namespace {
@@ -180,8 +184,9 @@ int build_host_scene(const rt_scene* scene, HostScene* hs) {
                     hs->box_fast.push_back((float)(((double)c.w2l[4 * r + 3] - ctr) * ih));
                 }
             }
-            // bounding sphere of the box in world space (T*R is rigid: the circumradius is |half extent|),
-            // padded by 1e-3 so that the test is conservative against the slab test's own rounding
+            // bounding sphere of the box in world space (T*R is rigid: the circumradius is |half extent|);
+            // the radius is stored un-padded here (negative = degenerate) and padded once the scene
+            // extent is known (end of this function)
             {
                 double ctr[3], r2 = 0.0;
                 for (int r = 0; r < 3; r++) {
@@ -192,7 +197,7 @@ int build_host_scene(const rt_scene* scene, HostScene* hs) {
                 for (int r = 0; r < 3; r++)
                     hs->box_cull.push_back((float)((double)c.l2w[4 * r + 0] * ctr[0] + (double)c.l2w[4 * r + 1] * ctr[1] +
                                                    (double)c.l2w[4 * r + 2] * ctr[2] + (double)c.l2w[4 * r + 3]));
-                hs->box_cull.push_back(degenerate ? -1e30f : (float)(r2 * 1.001 + 1e-12));
+                hs->box_cull.push_back(degenerate ? -1.0f : (float)std::sqrt(r2));
             }
         } else if (o.sphere_radius != -1.0f) {              // glsl:759
             c.kind = RT_KIND_SPHERE;
@@ -217,6 +222,76 @@ int build_host_scene(const rt_scene* scene, HostScene* hs) {
         bool lit = false;   // a light with zero diffuse and specular adds 0 shadowed or not (glsl:830-832)
         for (int k = 0; k < 4; k++) lit = lit || L.diffuse[k] != 0.0f || L.specular[k] != 0.0f;
         d.position[3] = lit ? 1.0f : 0.0f;
+    }
+    // Scene extent E: ray origins (hit points), lights and centres have coordinates up to ~E, so every
+    // difference of two of them carries an absolute FP32 rounding error up to ~E * 2^-23.  The bounding
+    // radii are padded by 5e-4 relative + 2e-6 * E absolute: far more than that rounding and than the
+    // slab test's own, so the bounding-sphere tests never reject a ray the exact test would accept.
+    double extent = 1.0;
+    for (size_t b = 0; b < hs->box_obj.size(); b++) {
+        const float* q = &hs->box_cull[4 * b];
+        extent = std::max(extent, std::sqrt((double)q[0] * q[0] + (double)q[1] * q[1] + (double)q[2] * q[2]) + std::fabs((double)q[3]));
+    }
+    for (size_t j = 0; j < hs->sph_obj.size(); j++) {
+        const float* q = &hs->sph[4 * j];
+        extent = std::max(extent, std::sqrt((double)q[0] * q[0] + (double)q[1] * q[1] + (double)q[2] * q[2]) + std::sqrt(std::fabs((double)q[3])));
+    }
+    for (const RtLightDev& L : hs->lights)
+        extent = std::max(extent, std::sqrt((double)L.position[0] * L.position[0] + (double)L.position[1] * L.position[1] +
+                                            (double)L.position[2] * L.position[2]));
+    const double abs_pad = 2e-6 * extent;
+    std::vector<double> box_rad(hs->box_obj.size());
+    for (size_t b = 0; b < hs->box_obj.size(); b++) {
+        box_rad[b] = hs->box_cull[4 * b + 3];                             // un-padded circumradius, < 0 = degenerate
+        const double rp = box_rad[b] * 1.0005 + abs_pad;
+        hs->box_cull[4 * b + 3] = box_rad[b] < 0.0 ? -1e30f : (float)(rp * rp * (1.0 + 1e-6));
+    }
+    // Per-light records for the shadow rays of large scenes (rt_kernel.cuh: lights_tile).  The shadow
+    // ray of light L starts at p + 0.01 n and runs along L - p (glsl:808-809), i.e. along the line
+    // through L shifted by 0.01 n, |n| = 1 (rigid box transforms, normalised sphere normals): growing
+    // the bounding radius by a further 0.0101 makes "the line through L along d meets the sphere" a
+    // conservative stand-in for "the ray's line meets the primitive".
+    std::vector<int> lit;
+    for (int j = 0; j < (int)hs->lights.size(); j++)
+        if (hs->lights[j].position[3] != 0.0f) lit.push_back(j);
+    hs->n_lit = (lit.size() >= 1 && lit.size() <= 3) ? (int)lit.size() : 0;
+    if (hs->n_lit > 0) {
+        const int n_hot = (int)(hs->box_obj.size() + hs->sph_obj.size());
+        const int tiles = (n_hot + 63) / 64;
+        hs->obj_lrec.assign((size_t)tiles * hs->n_lit * 64 * 4, 0.0f);
+        for (size_t k = 3; k < hs->obj_lrec.size(); k += 4) hs->obj_lrec[k] = 1e30f;   // padding: never passes
+        for (int h = 0; h < n_hot; h++) {
+            double c[3], rad;
+            const bool is_b = h < (int)hs->box_obj.size();
+            if (is_b) {
+                for (int r = 0; r < 3; r++) c[r] = hs->box_cull[4 * h + r];
+                if (box_rad[h] < 0.0) continue;                          // degenerate box: never hit
+                rad = box_rad[h];
+            } else {
+                const int j = h - (int)hs->box_obj.size();
+                for (int r = 0; r < 3; r++) c[r] = hs->sph[4 * j + r];
+                rad = std::sqrt((double)hs->sph[4 * j + 3]);
+            }
+            const double rp = rad * 1.0005 + 0.0101 + abs_pad;
+            // The shader's sphere quadratic (glsl:586-591) cancels catastrophically when the ray starts
+            // far from the sphere: its discriminant carries an error of ~2^-22 |o - c|^2 in squared-distance
+            // units and it then reports hits for lines that pass the sphere at some distance.  The record
+            // must let those through as well (the image has to stay identical), hence the E^2 term.
+            const double rp2 = rp * rp + (is_b ? 0.0 : 4e-6 * extent * extent);
+            for (int s2 = 0; s2 < hs->n_lit; s2++) {
+                const RtLightDev& L = hs->lights[lit[s2]];
+                float* rec = &hs->obj_lrec[(((size_t)(h / 64) * hs->n_lit + s2) * 64 + (h % 64)) * 4];
+                double oc2 = 0.0;
+                for (int r = 0; r < 3; r++) {
+                    const double oc = (double)L.position[r] - c[r];
+                    rec[r] = (float)oc;
+                    oc2 += oc * oc;
+                }
+                // rounded toward "pass": the float record must not be larger than the exact value
+                const double qc = oc2 - rp2;
+                rec[3] = (float)(qc - std::fabs(qc) * 1e-6 - 1e-12);
+            }
+        }
     }
     return RT_OK;
 }
@@ -282,7 +357,7 @@ int rt_destroy(rt_context* c) {
     if (!c) return RT_OK;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_sph.release();
+    c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_obj_lrec.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -322,6 +397,7 @@ int rt_upload_scene(rt_context* c, const rt_scene* scene) {
     CU(c->d_box_fast.reserve(hs.box_fast.size() + 4));
     CU(c->d_box_strict.reserve(hs.box_strict.size() + 4));
     CU(c->d_box_cull.reserve(hs.box_cull.size() + 4));
+    CU(c->d_obj_lrec.reserve(hs.obj_lrec.size() + 4));
     CU(c->d_sph.reserve(hs.sph.size() + 4));
     CU(c->d_box_obj.reserve(hs.box_obj.size() + 1));
     CU(c->d_sph_obj.reserve(hs.sph_obj.size() + 1));
@@ -334,6 +410,7 @@ int rt_upload_scene(rt_context* c, const rt_scene* scene) {
     CU(up(c->d_box_fast.p, hs.box_fast.data(), hs.box_fast.size() * 4));
     CU(up(c->d_box_strict.p, hs.box_strict.data(), hs.box_strict.size() * 4));
     CU(up(c->d_box_cull.p, hs.box_cull.data(), hs.box_cull.size() * 4));
+    CU(up(c->d_obj_lrec.p, hs.obj_lrec.data(), hs.obj_lrec.size() * 4));
     CU(up(c->d_sph.p, hs.sph.data(), hs.sph.size() * 4));
     CU(up(c->d_box_obj.p, hs.box_obj.data(), hs.box_obj.size() * 4));
     CU(up(c->d_sph_obj.p, hs.sph_obj.data(), hs.sph_obj.size() * 4));
@@ -344,6 +421,7 @@ int rt_upload_scene(rt_context* c, const rt_scene* scene) {
     c->n_box = (int)hs.box_obj.size();
     c->n_sph = (int)hs.sph_obj.size();
     c->n_lights = (int)hs.lights.size();
+    c->n_lit = hs.n_lit;
     c->max_depth = hs.max_depth;
     c->have_scene = true;
     return RT_OK;
@@ -392,6 +470,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.box_hot = reinterpret_cast<const float4*>(o.strict ? c->d_box_strict.p : c->d_box_fast.p);
     P.box_cull = reinterpret_cast<const float4*>(c->d_box_cull.p);
     P.sph_hot = reinterpret_cast<const float4*>(c->d_sph.p);
+    P.obj_lrec = reinterpret_cast<const float4*>(c->d_obj_lrec.p);
     P.box_obj = c->d_box_obj.p; P.sph_obj = c->d_sph_obj.p;
     P.cold = c->d_cold.p; P.lights = c->d_lights.p; P.cams = c->d_cams.p;
     P.counters = c->d_cnt.p;
@@ -405,8 +484,10 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.tiles_x = (width + 7) / 8; P.tiles_y = (band_rows + 3) / 4;
     // Large scenes (fast kernel): the slab test runs behind a conservative bounding-sphere test, and
     // only the 16-byte bounding-sphere records are staged / streamed (rt_kernel.cuh: boxes_tile_cull).
-    P.cull = (!o.strict && !o.no_cull) ? 1 : 0;
-    const size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : (P.cull ? 1 : RT_BOX_F4_FAST)) + P.n_sph) * 16;
+    P.cull = (!o.strict && !(o.no_cull & 1)) ? 1 : 0;
+    P.n_lit = (P.cull && !(o.no_cull & 2)) ? c->n_lit : 0;
+    size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : (P.cull ? 1 : RT_BOX_F4_FAST)) + P.n_sph) * 16;
+    if (P.n_lit > 0) hot_bytes += (size_t)((P.n_box + P.n_sph + 63) / 64) * P.n_lit * 64 * 16;
     P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin)
                                         : rt_fast::resident_limit_bytes(c->max_smem_optin)) ? 1 : 0;
 

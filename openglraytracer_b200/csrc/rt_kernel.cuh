@@ -241,6 +241,7 @@ constexpr int kScratchBytes = kQueueRays * 8 * 4 + 96 * 4;     // queue + occlus
 
 struct WarpCtx {
     uint32_t box_off4, sph_off4; // resident: float4 offsets of the staged hot lists in smem_f4
+    uint32_t lrec_off4;          // resident: float4 offset of the staged per-light records
     float* queue;                // [kQueueRays][8]
     int* occ;                    // [96]
     uint32_t buf_off4[2];        // streaming double buffer (float4 offsets in smem_f4)
@@ -513,6 +514,109 @@ __device__ __forceinline__ void spheres_tile(const RtParams& P, const float4* __
     }
 }
 
+// -------------------------------------------------------------------------
+// Shadow rays against per-light records (large scenes, 1..3 lit lights).
+// A shadow ray runs from p + 0.01 n along L - p (glsl:808-809): its line is the line
+// through p and the light L, shifted by 0.01 n.  So "the line through L along d meets
+// the primitive's bounding sphere grown by 0.0101" is a conservative test for "the ray's
+// line meets the bounding sphere", and it needs no per-pixel origin work: the host stores,
+// for every hot object (boxes then spheres) and every lit light, (L - c, |L - c|^2 - R'^2).
+// Per (ray, object): one 16-byte LDS + 3 FFMA/FMUL (d . oc) + 2 (discriminant) + compare,
+// against 21 instructions for the slab test; the exact test runs behind the warp vote.
+// Tiles hold kTileBox objects x n_lit records: tile t = [light 0: 64][light 1: 64]...
+// -------------------------------------------------------------------------
+__device__ __forceinline__ int n_lrec_tiles(const RtParams& P) { return (P.n_box + P.n_sph + kTileBox - 1) / kTileBox; }
+
+__device__ __forceinline__ void lrec_issue(const RtParams& P, WarpCtx& w, int t) {
+    const uint32_t bytes = (uint32_t)P.n_lit * kTileBox * 16u;
+    const void* src = P.obj_lrec + (size_t)t * P.n_lit * kTileBox;
+    const int b = t & 1;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(w.bar_addr[b]), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(w.buf_addr[b]), "l"(src), "r"(bytes), "r"(w.bar_addr[b]) : "memory");
+}
+template <bool SMEM>
+__device__ __forceinline__ const float4* lrec_acquire(const RtParams& P, WarpCtx& w, int t, int n_tiles) {
+    if (SMEM) return smem_f4 + w.lrec_off4 + (uint32_t)t * P.n_lit * kTileBox;
+    __syncwarp();
+    if (w.lane == 0 && t + 1 < n_tiles) lrec_issue(P, w, t + 1);
+    tile_wait(w, t & 1);
+    return smem_f4 + w.buf_off4[t & 1];
+}
+
+// exact sphere test (glsl:585-625) of hot sphere j for the rays in m (rare path)
+template <int R, bool COUNT>
+__device__ __forceinline__ void sphere_full_test(const RtParams& P, int j, unsigned m,
+                                                 const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                                 float (&best)[kShadowBatch], RtCounters& cnt) {
+    const float4 c = __ldg(P.sph_hot + j);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const bool mine = (m >> r) & 1u;
+        if (COUNT) cnt.sphere_tests += mine;
+        bool inside;
+        const float t = sphere_t(sphere_origin(c, o[r]), d[r], ray_q(d[r]), inside);
+        if (mine && t > 0.0f && t < best[r]) best[r] = t;
+    }
+}
+
+template <int R, bool COUNT>
+__device__ __forceinline__ void lights_tile(const RtParams& P, const float4* __restrict__ recs, int t,
+                                            const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                            float (&best)[kShadowBatch], const int (&src)[kShadowBatch],
+                                            RtCounters& cnt) {
+    constexpr int G = 4;
+    const int first = t * kTileBox;
+    const int n = min(kTileBox, P.n_box + P.n_sph - first);
+    float qe[R];
+    uint32_t sec[R];              // float4 offset of the ray's light section in the tile (slot = src % 3)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        qe[r] = __fmul_rn(__fmaf_rn(d[r].x, d[r].x, __fmaf_rn(d[r].y, d[r].y, __fmul_rn(d[r].z, d[r].z))), 0.9999f);
+        const int slot = src[r] >= 0 ? src[r] % kShadowBatch : 0;
+        sec[r] = (uint32_t)min(slot, P.n_lit - 1) * kTileBox;
+    }
+    for (int i = 0; i < n; i += G) {
+        float qf[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool live = best[r] >= 1.0f;
+            if (COUNT) cnt.cull_tests += live ? (unsigned long long)min(G, n - i) : 0ull;
+            qf[r] = live ? qe[r] : 1e30f;
+        }
+        bool any = false;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float4 c = recs[sec[r] + i + g];          // (L - centre, |L - centre|^2 - R'^2); padded tiles
+                const float hb = __fmaf_rn(d[r].x, c.x, __fmaf_rn(d[r].y, c.y, __fmul_rn(d[r].z, c.z)));
+                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qf[r], c.w));
+                any = any || disc >= 0.0f;
+            }
+        }
+        if (__any_sync(kFull, any)) {
+#pragma unroll 1
+            for (int g = 0; g < G && i + g < n; ++g) {
+                unsigned m = 0u;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const float4 c = recs[sec[r] + i + g];
+                    const float hb = __fmaf_rn(d[r].x, c.x, __fmaf_rn(d[r].y, c.y, __fmul_rn(d[r].z, c.z)));
+                    const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qe[r], c.w));
+                    if (best[r] >= 1.0f && disc >= 0.0f) m |= 1u << r;
+                }
+                if (__any_sync(kFull, m != 0u)) {
+                    const int idx = first + i + g;
+                    int unused[kShadowBatch];
+                    if (idx < P.n_box) box_full_test<R, true, false, COUNT>(P, idx, m, o, d, best, unused, cnt);
+                    else sphere_full_test<R, COUNT>(P, idx - P.n_box, m, o, d, best, cnt);
+                }
+            }
+        }
+    }
+}
+
 // One tile, dispatched on its kind.
 template <int R, bool ANYHIT, bool SHARED, bool COUNT, bool CULL>
 __device__ __forceinline__ void any_tile(const RtParams& P, const float4* recs, int t,
@@ -572,7 +676,7 @@ __device__ __forceinline__ void trace_closest(const RtParams& P, WarpCtx& w, V3 
 // with its own origin).  Dead rays therefore stop costing issue slots, and a warp
 // whose rays are all occluded leaves the object loop.
 // -------------------------------------------------------------------------
-template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
+template <bool SMEM, bool REPACK, bool COUNT, bool CULL, bool LREC>
 __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 so, const V3 (&sd)[kShadowBatch],
                                              float (&sb)[kShadowBatch], int n_slots, RtCounters& cnt) {
     V3 o[kShadowBatch], d[kShadowBatch];
@@ -583,7 +687,7 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
     bool shared = true;
     unsigned own_occ = 0u;
     const unsigned lt_mask = (1u << w.lane) - 1u;
-    const int n_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
+    const int n_tiles = LREC ? n_lrec_tiles(P) : n_box_tiles<CULL>(P) + n_sph_tiles(P);
     bool started = false;
 
     if (!REPACK) {
@@ -663,6 +767,15 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
             __syncwarp();
             r_cur = new_r;
             shared = false;
+        }
+        if (LREC) {
+            // per-light records: no origin work in the loop, so "shared" only matters to the re-pack above
+            if (!started) { if (!SMEM && w.lane == 0) lrec_issue(P, w, 0); started = true; }
+            const float4* lrecs = lrec_acquire<SMEM>(P, w, t, n_tiles);
+            if (r_cur == 3) lights_tile<3, COUNT>(P, lrecs, t, o, d, best, src, cnt);
+            else if (r_cur == 2) lights_tile<2, COUNT>(P, lrecs, t, o, d, best, src, cnt);
+            else lights_tile<1, COUNT>(P, lrecs, t, o, d, best, src, cnt);
+            continue;
         }
         if (!started) { tile_begin<SMEM, CULL>(P, w); started = true; }
         const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_tiles);
@@ -921,7 +1034,8 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                         sb[r] = 0.0f;
                     }
                 }
-                trace_shadow<SMEM, REPACK, COUNT, CULL>(P, w, so, sd, sb, n_slots, cnt);
+                if (REPACK && CULL && P.n_lit > 0) trace_shadow<SMEM, REPACK, COUNT, CULL, true>(P, w, so, sd, sb, n_slots, cnt);
+                else trace_shadow<SMEM, REPACK, COUNT, CULL, false>(P, w, so, sd, sb, n_slots, cnt);
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     if (shade && r < n_slots && !(sb[r] < 1.0f)) {
@@ -995,8 +1109,14 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
         w.box_off4 = 0u;
         w.sph_off4 = (uint32_t)nb4;
         off4 = (size_t)nb4 + ns4;
+        w.lrec_off4 = (uint32_t)off4;
+        if (CULL && P.n_lit > 0) {
+            const int nl4 = n_lrec_tiles(P) * P.n_lit * kTileBox;
+            for (int i = threadIdx.x; i < nl4; i += kThreads) smem_f4[off4 + i] = __ldg(P.obj_lrec + i);
+            off4 += (size_t)nl4;
+        }
     } else {
-        w.box_off4 = w.sph_off4 = 0u;
+        w.box_off4 = w.sph_off4 = w.lrec_off4 = 0u;
     }
     {
         float4* scratch = smem_f4 + off4 + (size_t)warp * (kScratchBytes / 16);
@@ -1139,7 +1259,11 @@ __global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOC
 
 // Launchers with C linkage-free, namespace-qualified names; called from rt_host.cpp.
 namespace RT_NS {
-inline size_t hot_smem_bytes(const RtParams& P, bool cull) { return ((size_t)P.n_box * (cull ? 1 : RT_BOX_F4) + (size_t)P.n_sph) * sizeof(float4); }
+inline size_t hot_smem_bytes(const RtParams& P, bool cull) {
+    size_t f4 = (size_t)P.n_box * (cull ? 1 : RT_BOX_F4) + (size_t)P.n_sph;
+    if (cull && P.n_lit > 0) f4 += (size_t)((P.n_box + P.n_sph + kTileBox - 1) / kTileBox) * P.n_lit * kTileBox;
+    return f4 * sizeof(float4);
+}
 inline size_t scratch_smem_bytes() { return (size_t)kWarps * kScratchBytes; }
 inline size_t stream_smem_bytes() { return (size_t)kWarps * (2 * kTileBytes + 16); }
 size_t resident_limit_bytes(int max_smem_optin);

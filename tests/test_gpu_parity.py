@@ -184,8 +184,10 @@ def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
     _, st_on = tracer.render(sc, cam, w, h, want_stats=True)
     _, st_off = tracer.render(sc, cam, w, h, want_stats=True, no_cull=True)
     on = tracer.render(sc, cam, w, h)                    # the shipped kernels (the counting twins are
-    off = tracer.render(sc, cam, w, h, no_cull=True)     # separate instantiations)
+    off = tracer.render(sc, cam, w, h, no_cull=1)        # separate instantiations)
     assert np.array_equal(on, off)
+    # bit 1: bounding-sphere test on, per-light shadow records off
+    assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=2))
     assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
     assert st_off["cull_tests"] == 0 and st_on["cull_tests"] > 0
     assert st_on["box_tests"] < st_off["box_tests"] // 4
@@ -233,7 +235,8 @@ def test_bounding_sphere_test_far_and_tiny_objects(tracer):
     for half in (11.0, 3000.0):
         sc = _far_scene(half)
         on = tracer.render(sc, cam, 320, 180)
-        assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=True))
+        assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=1))
+        assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=2))
         ref = ob.render(sc, cam, 320, 180)
         _check(tracer.render(sc, cam, 320, 180, strict=True), ref, "far/tiny objects strict", need_edges=False)
         if half < 100.0:
