@@ -37,12 +37,12 @@ static_assert(sizeof(RtCold) == 64 * 4, "cold record must be 256 bytes");
 namespace rt_fast {
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
-size_t resident_limit_bytes(int max_smem_optin);
+size_t resident_limit_bytes(int max_smem_optin, bool cull);
 }
 namespace rt_strict {
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
-size_t resident_limit_bytes(int max_smem_optin);
+size_t resident_limit_bytes(int max_smem_optin, bool cull);
 }
 
 namespace {
@@ -488,8 +488,8 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.n_lit = (P.cull && !(o.no_cull & 2)) ? c->n_lit : 0;
     size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : (P.cull ? 1 : RT_BOX_F4_FAST)) + P.n_sph) * 16;
     if (P.n_lit > 0) hot_bytes += (size_t)((P.n_box + P.n_sph + 63) / 64) * P.n_lit * 64 * 16;
-    P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin)
-                                        : rt_fast::resident_limit_bytes(c->max_smem_optin)) ? 1 : 0;
+    P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin, false)
+                                        : rt_fast::resident_limit_bytes(c->max_smem_optin, P.cull != 0)) ? 1 : 0;
 
     if (o.out_is_device) {
         P.out = (uint8_t*)out_rgba;

@@ -51,6 +51,9 @@ namespace RT_NS {
 #ifndef RT_MIN_BLOCKS
 #define RT_MIN_BLOCKS 2          // large scenes: the object loops are issue-bound, 16 warps/SM suffice
 #endif
+#ifndef RT_MIN_BLOCKS_CULL
+#define RT_MIN_BLOCKS_CULL 2     // large scenes behind the bounding-sphere tests: short dependent chains on 16-byte LDS
+#endif                           // results, latency-bound at 16 warps/SM -> 24 warps/SM (85 registers; shading spills a little)
 #ifndef RT_MIN_BLOCKS_SMALL
 #define RT_MIN_BLOCKS_SMALL 3    // small scenes: short loops, latency-bound shading -> 24 warps/SM
 #endif
@@ -252,6 +255,14 @@ struct WarpCtx {
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// 16-byte shared-memory load by 32-bit shared address.  volatile: the loads of one group of records
+// stay where they are written, ahead of the arithmetic (ptxas otherwise issues each load right before
+// its dependent chain and the loop runs at shared-memory latency).
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
 
 // CULL: the box tiles hold 16-byte bounding-sphere records (kTileSph per tile); the 48-byte slab
 // records stay in global memory / L2 and are read only when some lane passes the bounding-sphere test.
@@ -390,35 +401,48 @@ __device__ __forceinline__ void box_full_test(const RtParams& P, int idx, unsign
 
 template <int R, bool ANYHIT, bool SHARED, bool COUNT>
 __device__ __forceinline__ void boxes_tile_cull(const RtParams& P, const float4* __restrict__ recs, int n, int base,
-                                                const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
-                                                float (&best)[kShadowBatch], int (&bidx)[kShadowBatch],
+                                                const V3 (&o_in)[kShadowBatch], const V3 (&d_in)[kShadowBatch],
+                                                float (&best_io)[kShadowBatch], int (&bidx_io)[kShadowBatch],
                                                 RtCounters& cnt) {
-    constexpr int G = 4;                 // boxes per warp vote
-    float qe[R];
+    // Out of line on purpose (see lights_tile): own register allocation, loads issued per group.
+    V3 o[kShadowBatch], d[kShadowBatch];
+    float best[kShadowBatch]; int bidx[kShadowBatch];
 #pragma unroll
-    for (int r = 0; r < R; ++r)
+    for (int r = 0; r < kShadowBatch; ++r) { o[r] = o_in[r]; d[r] = d_in[r]; best[r] = best_io[r]; bidx[r] = bidx_io[r]; }
+    constexpr int G = R == 1 ? 8 : 4;    // boxes per warp vote; G record loads in flight
+    float qe[R], qf[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
         qe[r] = __fmul_rn(__fmaf_rn(d[r].x, d[r].x, __fmaf_rn(d[r].y, d[r].y, __fmul_rn(d[r].z, d[r].z))), 0.9999f);
-    for (int i = 0; i < n; i += G) {
         // Fast path: G boxes, one predicate, one vote.  A ray that is no longer live (occluded shadow
         // ray, idle lane) gets qa = 1e30 so that it fails the test unless its origin lies inside the
         // sphere; the slow path below re-checks liveness exactly, so that only costs a rare detour.
-        float qf[R];
+        qf[r] = (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) ? qe[r] : 1e30f;   // refreshed after every slow path
+    }
+    const uint32_t ra = smem_addr(recs);
+    // Software pipeline: the records of group i + G are loaded while group i is tested.  A record
+    // past n (read from the padding / the next list) can only cause a detour through the slow path.
+    float4 cn[G];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const bool live = ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
-            if (COUNT) cnt.cull_tests += live ? (unsigned long long)min(G, n - i) : 0ull;
-            qf[r] = live ? qe[r] : 1e30f;
+    for (int g = 0; g < G; ++g) cn[g] = lds128(ra + (uint32_t)g * 16u);
+    for (int i = 0; i < n; i += G) {
+        if (COUNT) {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                cnt.cull_tests += (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) ? (unsigned long long)min(G, n - i) : 0ull;
         }
+        float4 c[G];
+        const uint32_t nxt = (uint32_t)(i + G < n ? i + G : i) * 16u;      // last group: a harmless re-load
+#pragma unroll
+        for (int g = 0; g < G; ++g) { c[g] = cn[g]; cn[g] = lds128(ra + nxt + (uint32_t)g * 16u); }
         bool any = false;
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-            // a record past n (the buffers are padded to a multiple of G records) can only cause a detour
-            const float4 c = recs[i + g];
             SphO so;
-            if (SHARED) so = sphere_origin(c, o[0]);
+            if (SHARED) so = sphere_origin(c[g], o[0]);
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                if (!SHARED) so = sphere_origin(c, o[r]);
+                if (!SHARED) so = sphere_origin(c[g], o[r]);
                 const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
                 const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qf[r], so.qc));
                 any = any || disc >= 0.0f;
@@ -443,8 +467,12 @@ __device__ __forceinline__ void boxes_tile_cull(const RtParams& P, const float4*
                 if (__any_sync(kFull, m != 0u))
                     box_full_test<R, ANYHIT, SHARED, COUNT>(P, base + i + g, m, o, d, best, bidx, cnt);
             }
+#pragma unroll
+            for (int r = 0; r < R; ++r) qf[r] = (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) ? qe[r] : 1e30f;
         }
     }
+#pragma unroll
+    for (int r = 0; r < R; ++r) { best_io[r] = best[r]; bidx_io[r] = bidx[r]; }
 }
 
 template <int R, bool ANYHIT, bool SHARED, bool COUNT, bool CULL>
@@ -562,36 +590,58 @@ __device__ __forceinline__ void sphere_full_test(const RtParams& P, int j, unsig
 
 template <int R, bool COUNT>
 __device__ __forceinline__ void lights_tile(const RtParams& P, const float4* __restrict__ recs, int t,
-                                            const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
-                                            float (&best)[kShadowBatch], const int (&src)[kShadowBatch],
+                                            const V3 (&o_in)[kShadowBatch], const V3 (&d_in)[kShadowBatch],
+                                            float (&best_io)[kShadowBatch], const int (&src)[kShadowBatch],
                                             RtCounters& cnt) {
-    constexpr int G = 4;
+    // Out of line on purpose: the caller's shading state (some 60 live values) stays out of this
+    // function's register allocation, so the record loads of a group are issued together.  The rays
+    // are copied into registers here (the reference parameters live in the caller's stack frame).
+    V3 o[kShadowBatch], d[kShadowBatch];
+    float best[kShadowBatch];
+#pragma unroll
+    for (int r = 0; r < kShadowBatch; ++r) { o[r] = o_in[r]; d[r] = d_in[r]; best[r] = best_io[r]; }
+    constexpr int G = R == 1 ? 8 : 4;          // objects per warp vote; G * R record loads in flight
     const int first = t * kTileBox;
     const int n = min(kTileBox, P.n_box + P.n_sph - first);
-    float qe[R];
+    float qe[R], qf[R];
     uint32_t sec[R];              // float4 offset of the ray's light section in the tile (slot = src % 3)
+    uint32_t ra[R];               // shared address of that section
+    const uint32_t base = smem_addr(recs);
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         qe[r] = __fmul_rn(__fmaf_rn(d[r].x, d[r].x, __fmaf_rn(d[r].y, d[r].y, __fmul_rn(d[r].z, d[r].z))), 0.9999f);
         const int slot = src[r] >= 0 ? src[r] % kShadowBatch : 0;
         sec[r] = (uint32_t)min(slot, P.n_lit - 1) * kTileBox;
+        ra[r] = base + sec[r] * 16u;
+        qf[r] = best[r] >= 1.0f ? qe[r] : 1e30f;     // refreshed after every slow path (the only place a ray dies)
+    }
+    // Software pipeline: the records of group i + G are loaded while group i is tested (the loads
+    // cannot sink below the loop's back edge, so they overlap the arithmetic of the current group).
+    float4 cn[G][R];                                 // (L - centre, |L - centre|^2 - R'^2); the tiles are padded
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) cn[g][r] = lds128(ra[r] + (uint32_t)g * 16u);
     }
     for (int i = 0; i < n; i += G) {
-        float qf[R];
+        if (COUNT) {
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const bool live = best[r] >= 1.0f;
-            if (COUNT) cnt.cull_tests += live ? (unsigned long long)min(G, n - i) : 0ull;
-            qf[r] = live ? qe[r] : 1e30f;
+            for (int r = 0; r < R; ++r) cnt.cull_tests += best[r] >= 1.0f ? (unsigned long long)min(G, n - i) : 0ull;
+        }
+        float4 c[G][R];
+        const uint32_t nxt = (uint32_t)min(i + G, kTileBox - G) * 16u;     // last group: a harmless re-load
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) { c[g][r] = cn[g][r]; cn[g][r] = lds128(ra[r] + nxt + (uint32_t)g * 16u); }
         }
         bool any = false;
 #pragma unroll
         for (int g = 0; g < G; ++g) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                const float4 c = recs[sec[r] + i + g];          // (L - centre, |L - centre|^2 - R'^2); padded tiles
-                const float hb = __fmaf_rn(d[r].x, c.x, __fmaf_rn(d[r].y, c.y, __fmul_rn(d[r].z, c.z)));
-                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qf[r], c.w));
+                const float hb = __fmaf_rn(d[r].x, c[g][r].x, __fmaf_rn(d[r].y, c[g][r].y, __fmul_rn(d[r].z, c[g][r].z)));
+                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qf[r], c[g][r].w));
                 any = any || disc >= 0.0f;
             }
         }
@@ -613,8 +663,12 @@ __device__ __forceinline__ void lights_tile(const RtParams& P, const float4* __r
                     else sphere_full_test<R, COUNT>(P, idx - P.n_box, m, o, d, best, cnt);
                 }
             }
+#pragma unroll
+            for (int r = 0; r < R; ++r) qf[r] = best[r] >= 1.0f ? qe[r] : 1e30f;
         }
     }
+#pragma unroll
+    for (int r = 0; r < R; ++r) best_io[r] = best[r];
 }
 
 // One tile, dispatched on its kind.
@@ -1093,7 +1147,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 // frames (tile index -> frame, tile row, tile column).
 // -------------------------------------------------------------------------
 template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
-__global__ void __launch_bounds__(kThreads, REPACK ? RT_MIN_BLOCKS : RT_MIN_BLOCKS_SMALL) render_kernel(const __grid_constant__ RtParams P) {
+__global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL : RT_MIN_BLOCKS) : RT_MIN_BLOCKS_SMALL) render_kernel(const __grid_constant__ RtParams P) {
     // dynamic shared memory: [hot scene (resident only)] [per-warp scratch] [per-warp tile buffers + barriers (streaming only)]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpCtx w;
@@ -1266,7 +1320,7 @@ inline size_t hot_smem_bytes(const RtParams& P, bool cull) {
 }
 inline size_t scratch_smem_bytes() { return (size_t)kWarps * kScratchBytes; }
 inline size_t stream_smem_bytes() { return (size_t)kWarps * (2 * kTileBytes + 16); }
-size_t resident_limit_bytes(int max_smem_optin);
+size_t resident_limit_bytes(int max_smem_optin, bool cull);
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
 }
