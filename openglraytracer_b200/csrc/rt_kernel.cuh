@@ -485,38 +485,75 @@ __device__ __forceinline__ void spheres_tile(const RtParams& P, const float4* __
     for (int r = 0; r < R; ++r) q[r] = ray_q(d[r]);
 #if !RT_STRICT
     if (CULL) {
-        // Large scenes: the discriminant of glsl:591 first (5 FP32 instructions per ray); the roots
-        // are computed only when some lane of the warp has a non-negative one.  Same expressions as
-        // sphere_t(), evaluated in two steps, so the result is identical.
-#pragma unroll 4
-        for (int j = 0; j < n; ++j) {
-            const float4 c = recs[j];
-            SphO so;
-            if (SHARED) so = sphere_origin(c, o[0]);
-            float hb[R], disc[R];
+        // Large scenes: the discriminant of glsl:591 first (5 FP32 instructions per ray), G spheres per
+        // warp vote, records software-pipelined like boxes_tile_cull; the roots are computed only for a
+        // sphere some lane has a non-negative discriminant for.  Same expressions as sphere_t(),
+        // evaluated in two steps, so the result is identical.  A dead ray tests with qa = 1e30.
+        constexpr int G = R == 1 ? 8 : 4;
+        float qf[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) qf[r] = (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) ? q[r].qa : 1e30f;
+        const uint32_t ra = smem_addr(recs);
+        float4 cn[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) cn[g] = lds128(ra + (uint32_t)g * 16u);
+        for (int j0 = 0; j0 < n; j0 += G) {
+            if (COUNT) {
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    cnt.cull_tests += (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) ? (unsigned long long)min(G, n - j0) : 0ull;
+            }
+            float4 c[G];
+            const uint32_t nxt = (uint32_t)(j0 + G < n ? j0 + G : j0) * 16u;
+#pragma unroll
+            for (int g = 0; g < G; ++g) { c[g] = cn[g]; cn[g] = lds128(ra + nxt + (uint32_t)g * 16u); }
             bool any = false;
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if (!SHARED) so = sphere_origin(c, o[r]);
-                const bool live = ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
-                if (COUNT) cnt.cull_tests += live;
-                hb[r] = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
-                disc[r] = __fmaf_rn(hb[r], hb[r], -__fmul_rn(q[r].qa, so.qc));
-                any = any || (live && disc[r] >= 0.0f);
-            }
-            if (__any_sync(kFull, any)) {
+            for (int g = 0; g < G; ++g) {
+                SphO so;
+                if (SHARED) so = sphere_origin(c[g], o[0]);
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    if (COUNT) cnt.sphere_tests += (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) && disc[r] >= 0.0f;
-                    const float sq = sqrt_approx(fmaxf(disc[r], 0.0f));
-                    const float tn = __fmul_rn(-hb[r] - sq, q[r].iqa);
-                    const float tf = __fmul_rn(sq - hb[r], q[r].iqa);
-                    const float t = (disc[r] < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
-                    if (t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = P.n_box + base + j; }
-                    else if (!ANYHIT && t == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
-                        if (__ldg(P.sph_obj + base + j) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + j;
+                    if (!SHARED) so = sphere_origin(c[g], o[r]);
+                    const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                    const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qf[r], so.qc));
+                    any = any || disc >= 0.0f;
+                }
+            }
+            if (__any_sync(kFull, any)) {
+#pragma unroll 1
+                for (int g = 0; g < G && j0 + g < n; ++g) {
+                    const int j = j0 + g;
+                    const float4 cc = recs[j];
+                    SphO so;
+                    if (SHARED) so = sphere_origin(cc, o[0]);
+                    float hb[R], disc[R];
+                    bool anyg = false;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        if (!SHARED) so = sphere_origin(cc, o[r]);
+                        const bool live = ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f);
+                        hb[r] = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                        disc[r] = __fmaf_rn(hb[r], hb[r], -__fmul_rn(q[r].qa, so.qc));
+                        anyg = anyg || (live && disc[r] >= 0.0f);
+                    }
+                    if (__any_sync(kFull, anyg)) {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            if (COUNT) cnt.sphere_tests += (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) && disc[r] >= 0.0f;
+                            const float sq = sqrt_approx(fmaxf(disc[r], 0.0f));
+                            const float tn = __fmul_rn(-hb[r] - sq, q[r].iqa);
+                            const float tf = __fmul_rn(sq - hb[r], q[r].iqa);
+                            const float t = (disc[r] < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
+                            if (t > 0.0f && t < best[r]) { best[r] = t; if (!ANYHIT) bidx[r] = P.n_box + base + j; }
+                            else if (!ANYHIT && t == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
+                                if (__ldg(P.sph_obj + base + j) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + j;
+                            }
+                        }
                     }
                 }
+#pragma unroll
+                for (int r = 0; r < R; ++r) qf[r] = (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f)) ? q[r].qa : 1e30f;
             }
         }
         return;
