@@ -56,7 +56,7 @@ WORKLOADS = {
 }
 BATCH_FRAMES = 256
 DEFAULT_WORKLOAD = "builtin_1080p_d4"
-METRIC = "Mrays/s (rays x bounces), built-in scene 1080p"
+METRIC = "Mrays/s (rays x bounces)"
 UNIT = "Mrays/s"
 
 # Algorithmic FP32 flops per unit of work (add/sub/mul/min/max/cmp/div/sqrt = 1, FMA = 2;

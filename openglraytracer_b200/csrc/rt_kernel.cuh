@@ -375,6 +375,66 @@ __device__ __forceinline__ void boxes_tile(const float4* __restrict__ recs, int 
 // every ray meets every object (glsl:744), in original order.  Cost: 5 FP32 instructions per
 // (ray, box) instead of 21; the 48-byte slab record is read from global/L2 only behind the vote.
 // -------------------------------------------------------------------------
+// boxes_tile for the large-scene kernels without the bounding-sphere test (rt_options.no_cull, and the
+// strict kernel's large scenes): two boxes per iteration, the records of the next two software-
+// pipelined (shared-memory latency overlaps the 40-odd instructions of the current pair).
+template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+__device__ __forceinline__ void boxes_tile_pipe(const float4* __restrict__ recs, int n, int base,
+                                                const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
+                                                float (&best)[kShadowBatch], int (&bidx)[kShadowBatch],
+                                                unsigned long long& n_tests) {
+    constexpr int G = 2;
+    constexpr uint32_t kRecBytes = RT_BOX_F4 * 16u;
+    const uint32_t ra = smem_addr(recs);
+    float4 nx[G][RT_BOX_F4];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+#pragma unroll
+        for (int k = 0; k < RT_BOX_F4; ++k) nx[g][k] = lds128(ra + (uint32_t)g * kRecBytes + (uint32_t)k * 16u);
+    }
+    for (int i = 0; i < n; i += G) {
+        float4 rec[G][RT_BOX_F4];
+        const uint32_t nxt = (uint32_t)(i + G < n ? i + G : i) * kRecBytes;     // last pair: a harmless re-load
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+#pragma unroll
+            for (int k = 0; k < RT_BOX_F4; ++k) {
+                rec[g][k] = nx[g][k];
+                nx[g][k] = lds128(ra + nxt + (uint32_t)g * kRecBytes + (uint32_t)k * 16u);
+            }
+        }
+        float tn[G][R], tf[G][R];
+        bool cand = false;
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            V3 so;
+            if (SHARED) so = box_origin(rec[g], o[0]);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (COUNT) n_tests += (i + g < n) && (ANYHIT ? (best[r] >= 1.0f) : (best[r] > 0.0f));
+                if (!SHARED) so = box_origin(rec[g], o[r]);
+                Slabs s; V3 ld;
+                box_slabs(rec[g], so, d[r], tn[g][r], tf[g][r], s, ld);
+                cand = cand || !box_reject(tn[g][r], tf[g][r]);
+            }
+        }
+        if (__any_sync(kFull, cand)) {
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const float t = box_pick(tn[g][r], tf[g][r]);
+                    // i + g < n: the pair may reach one record past the list (padding / the next list)
+                    if (i + g < n && !box_reject(tn[g][r], tf[g][r]) && t > 0.0f && t < best[r]) {
+                        best[r] = t;
+                        if (!ANYHIT) bidx[r] = base + i + g;
+                    }
+                }
+            }
+        }
+    }
+}
+
 // The slab test of box `idx` for the rays whose bit is set in pm (rare path, kept out of the unrolled loop).
 template <int R, bool ANYHIT, bool SHARED, bool COUNT>
 __device__ __forceinline__ void box_full_test(const RtParams& P, int idx, unsigned pm,
@@ -718,7 +778,8 @@ __device__ __forceinline__ void any_tile(const RtParams& P, const float4* recs, 
         const int first = t * box_tile_n<CULL>();
         const int n = min(box_tile_n<CULL>(), P.n_box - first);
         if (CULL) boxes_tile_cull<R, ANYHIT, SHARED, COUNT>(P, recs, n, first, o, d, best, bidx, cnt);
-        else boxes_tile<R, ANYHIT, SHARED, COUNT>(recs, n, first, o, d, best, bidx, cnt.box_tests);
+        else if (RT_STRICT) boxes_tile<R, ANYHIT, SHARED, COUNT>(recs, n, first, o, d, best, bidx, cnt.box_tests);
+        else boxes_tile_pipe<R, ANYHIT, SHARED, COUNT>(recs, n, first, o, d, best, bidx, cnt.box_tests);
     } else {
         const int first = (t - nbt) * kTileSph;
         spheres_tile<R, ANYHIT, SHARED, COUNT, CULL>(P, recs, min(kTileSph, P.n_sph - first), first, o, d, best, bidx, cnt);
