@@ -343,9 +343,11 @@ def run_gpu(args, wl_name, wl):
                  "byte_identical_to_single_gpu": same}
         # fused gather: every rank's kernel stores its band straight into rank 0's frame (CUDA IPC, NVLink)
         try:
-            for label, bset in (("peer_store", cost_bands),
+            for label, bset in (("peer_store", cost_bands), ("peer_store_feedback_bands", None),
                                 ("peer_store_equal_height_bands", [row_band(r, world, h) for r in range(world)])):
-                pf = PeerFrame(tracer, w, h, rank, world, dev, bands=bset)
+                pf = PeerFrame(tracer, w, h, rank, world, dev, bands=bset or cost_bands)
+                if bset is None:     # three feedback steps on the measured per-band times
+                    bset = pf.autotune(None, cam, cost_bands, iters=3, spp=spp)
                 for _ in range(3):
                     pf.render(None, cam, spp=spp)
                 barrier()
@@ -363,7 +365,7 @@ def run_gpu(args, wl_name, wl):
                 bands[label] = {"ms_per_frame": ms_p, "value": rays_per_frame / (ms_p * 1e-3) / 1e6,
                                 "collective": "none on the data path: kernels store into rank 0's frame over "
                                               "NVLink (CUDA IPC mapping), one 4-byte all-reduce as completion flag",
-                                "byte_identical_to_single_gpu": same_p}
+                                "bands": str(bset), "byte_identical_to_single_gpu": same_p}
         except Exception as exc:   # IPC refused (container policy): the NCCL gather above stands
             bands["peer_store"] = {"unavailable": repr(exc)[:200]}
 

@@ -49,6 +49,18 @@ def balanced_row_bands(row_cost, world, align=4):
     return [(cuts[r], cuts[r + 1]) for r in range(world)]
 
 
+def refine_row_bands(bands, band_ms, height, align=4):
+    """One feedback step: given the measured render time of every band, re-cut the frame so that the
+    bands would take equal time if cost were uniform inside each old band (piecewise-constant cost
+    density band_ms[r] / rows_r).  Two or three steps on a static view converge; in an animation the
+    previous frame's times play the same role."""
+    cost = [0.0] * height
+    for (a, b), ms in zip(bands, band_ms):
+        for y in range(a, b):
+            cost[y] = float(ms) / max(1, b - a)
+    return balanced_row_bands(cost, len(bands), align)
+
+
 def probe_row_cost(raytracer, scene, camera, width, height, spp=1, strips=72, shrink=8):
     """Per-row cost estimate for balanced_row_bands: the reference ray count (rt_stats.rays) of
     `strips` horizontal strips rendered at 1/shrink of the width with the counting kernel (a few
@@ -205,6 +217,33 @@ class PeerFrame:
             dist.all_reduce(self._flag, group=self.group)
         cur.wait_stream(self.stream)
         return self.frame
+
+    def set_bands(self, bands):
+        self.y0, self.y1 = bands[self.rank]
+
+    def autotune(self, scene, camera, bands, iters=3, **kw):
+        """Feedback balancing of the contiguous bands: render, all-gather the per-rank band times
+        (CUDA events on the render stream), re-cut (refine_row_bands); returns the final bands.  The
+        time exchange is a tiny all-gather outside the frame's data path."""
+        bands = list(bands)
+        for _ in range(iters):
+            self.set_bands(bands)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            cur = torch.cuda.current_stream(self.device)
+            self.stream.wait_stream(cur)
+            for k in range(2):          # first pass warms up, second is timed
+                if k == 1:
+                    e0.record(self.stream)
+                self.rt.render(scene, camera, self.width, self.height, y0=self.y0, y1=self.y1, band_only=False,
+                               out_device_ptr=self.ptr, async_=True, stream=self.stream.cuda_stream, **kw)
+            e1.record(self.stream)
+            self.stream.synchronize()
+            mine = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float32, device=self.device)
+            every = [torch.zeros_like(mine) for _ in range(self.world)]
+            dist.all_gather(every, mine, group=self.group)
+            bands = refine_row_bands(bands, [float(t.item()) for t in every], self.height)
+        self.set_bands(bands)
+        return bands
 
     def close(self):
         torch.cuda.synchronize(self.device)

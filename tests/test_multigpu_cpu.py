@@ -105,3 +105,22 @@ def test_uneven_band_gather_is_byte_identical(tmp_path):
     out = str(tmp_path / "frame.npy")
     mp.spawn(_worker_uneven, args=(2, _free_port(), w, h, bands, out), nprocs=2, join=True)
     assert np.array_equal(np.load(out), ob.render(ob.builtin_scene(0.2, 1), ob.builtin_camera(0.2), w, h))
+
+
+def test_feedback_refinement_converges_on_a_synthetic_cost():
+    from openglraytracer_b200.multigpu import refine_row_bands, row_band
+    h, g = 2160, 8
+    y = np.arange(h)
+    true_cost = 1.0 + 4.0 * np.exp(-((y - 500) / 300.0) ** 2) + (y < 200) * 2.0     # rays per row, say
+
+    def times(bs):
+        return [float(true_cost[a:b].sum()) for a, b in bs]
+
+    bands = [row_band(r, g, h) for r in range(g)]
+    imbalance0 = max(times(bands)) / (true_cost.sum() / g)
+    for _ in range(4):
+        bands = refine_row_bands(bands, times(bands), h)
+        assert bands[0][0] == 0 and bands[-1][1] == h and all(b > a for a, b in bands)
+        assert all(bands[i][1] == bands[i + 1][0] for i in range(g - 1))
+    imbalance = max(times(bands)) / (true_cost.sum() / g)
+    assert imbalance0 > 1.5 and imbalance < 1.05
