@@ -55,6 +55,9 @@ WORKLOADS = {
     "batch256_1024_d4": ("batch", 5, 1024, 1024, 1, 4),
 }
 BATCH_FRAMES = 256
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel, from the committed
+# `ncu --set full` captures (profiles/r1_ncu_full_*.txt); the 8.3 MB frame mostly stays in the 126 MB L2.
+NCU_DRAM_BYTES = {"builtin_1080p_d4": 62720 + 683520, "scaled_1k_1080p_d0": 1194752 + 2989568}
 DEFAULT_WORKLOAD = "builtin_1080p_d4"
 METRIC = "Mrays/s (rays x bounces)"
 UNIT = "Mrays/s"
@@ -390,7 +393,9 @@ def run_gpu(args, wl_name, wl):
                     "checksum": checksum},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": achieved / peak_tf, "traffic": None,
+                         "frac": achieved / peak_tf, "traffic": NCU_DRAM_BYTES.get(wl_name),
+                         "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/); algorithmic bytes = the "
+                                         "%d-byte frame + a few KB of scene: FP32-issue bound, not HBM" % (nfr * w * h * 4),
                          "peak_source": "FP32 FMA-chain microbenchmark in this run (MEASURED_PEAKS.json has no FP32 "
                                         "figure); nominal 148 SM x 128 x 2 x 1.965 GHz = 74.4",
                          "algorithmic_flops_per_launch": flops_per_frame, "kernel_ms": kernel_ms,
