@@ -218,7 +218,7 @@ def run_gpu(args, wl_name, wl):
     import torch
     import torch.distributed as dist
     import openglraytracer_b200 as rt
-    from openglraytracer_b200.multigpu import (BandRenderer, PeerFrame, balanced_row_bands, frame_block,
+    from openglraytracer_b200.multigpu import (BandRenderer, PeerFrame, balanced_row_bands, frame_stride_set,
                                                  probe_row_cost, row_band)
 
     rank = int(os.environ.get("RANK", "0"))
@@ -238,11 +238,11 @@ def run_gpu(args, wl_name, wl):
     batch = kind == "batch"
     nfr = 1
     cams = cam
-    if batch:   # whole frames per rank: poses [k0, k1) of the 256-pose turntable (glsl:343-358 orbit)
-        k0, k1 = frame_block(rank, world, BATCH_FRAMES)
+    if batch:   # whole frames per rank: poses k = rank (mod world) of the 256-pose turntable (glsl:343-358 orbit)
+        mine = frame_stride_set(rank, world, BATCH_FRAMES)
         poses = rt.turntable_cameras(BATCH_FRAMES)
-        nfr = k1 - k0
-        cams = (rt.Camera * nfr)(*[poses[k] for k in range(k0, k1)])
+        nfr = len(mine)
+        cams = (rt.Camera * nfr)(*[poses[k] for k in mine])
     tracer = rt.Raytracer(local)
     # a real (non-NULL) stream: the C ABI treats a NULL stream as "the context's own stream"
     stream = torch.cuda.Stream(dev)

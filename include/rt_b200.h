@@ -178,6 +178,17 @@ int rt_upload_scene(rt_context* ctx, const rt_scene* scene);
 int rt_render_uploaded(rt_context* ctx, const rt_camera* cameras, int n_frames,
                        void* out_rgba, int width, int height, const rt_options* opts);
 
+/* Where the per-object prologue of rt_upload_scene runs (the matrices the shader rebuilds per test,
+ * glsl:650-652, 718): on the host, or as device kernels from the raw objects (large animated scenes:
+ * 8.6 MB of objects over PCIe instead of 27 MB of records at 64k objects, no host trigonometry).
+ * AUTO = device from RT_PROLOGUE_DEVICE_MIN_OBJECTS objects up.  The strict kernel always uses the
+ * host run (a strict render after a device prologue re-runs it from a kept copy of the scene). */
+#define RT_PROLOGUE_AUTO   0
+#define RT_PROLOGUE_HOST   1
+#define RT_PROLOGUE_DEVICE 2
+#define RT_PROLOGUE_DEVICE_MIN_OBJECTS 2048
+int rt_set_prologue(rt_context* ctx, int mode);
+
 /* The shader's hard-coded data as a function of its one real uniform `time`
  * (glsl:4): objects (glsl:261-321), lights (glsl:199-224), camera (glsl:334-364).
  * objects must have room for 5 rt_object, lights for 3 rt_light.  scene->max_depth

@@ -72,7 +72,7 @@ EXPORTS = [
     "rt_render_batch", "rt_upload_scene", "rt_render_uploaded", "rt_builtin_scene", "rt_builtin_camera",
     "rt_orbit_camera", "rt_scaled_scene", "rt_write_ppm", "rt_write_raw", "rt_fp32_peak_tflops",
     "rt_ipc_export", "rt_ipc_import", "rt_ipc_close", "rt_device_alloc", "rt_device_free",
-    "rt_scene_save", "rt_scene_load", "rt_scene_file_scene", "rt_scene_file_camera", "rt_scene_file_free",
+    "rt_set_prologue", "rt_scene_save", "rt_scene_load", "rt_scene_file_scene", "rt_scene_file_camera", "rt_scene_file_free",
 ]
 
 _lib = None
@@ -117,6 +117,7 @@ def lib():
     L.rt_ipc_close.argtypes = [vp]
     L.rt_device_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     L.rt_device_free.argtypes = [vp]
+    L.rt_set_prologue.argtypes = [vp, C.c_int]
     L.rt_scene_save.argtypes = [C.c_char_p, C.POINTER(Scene), C.POINTER(Camera)]
     L.rt_scene_load.argtypes = [C.c_char_p, C.POINTER(vp)]
     L.rt_scene_file_scene.argtypes = [vp]

@@ -154,6 +154,11 @@ class Raytracer:
     def __exit__(self, *a):
         self.close()
 
+    def set_prologue(self, mode):
+        """Where the per-object prologue runs: "auto" (device from 2048 objects), "host", "device"."""
+        code = {"auto": 0, "host": 1, "device": 2}[mode]
+        check(self._lib.rt_set_prologue(self._ctx, code), "rt_set_prologue")
+
     def synchronize(self):
         check(self._lib.rt_synchronize(self._ctx), "rt_synchronize")
 

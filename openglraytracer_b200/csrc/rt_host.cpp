@@ -26,6 +26,7 @@
 #include "../../include/rt_b200.h"
 #include "rt_device.h"
 #include "rt_hostmath.h"
+#include "rt_prologue_math.h"
 
 static_assert(RT_MAX_DEPTH == RT_MAX_DEPTH_DEV, "depth limits out of sync");
 static_assert(sizeof(rt_material) == 20 * 4, "rt_material must be 20 words (glsl:56-69)");
@@ -38,6 +39,12 @@ namespace rt_fast {
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
 size_t resident_limit_bytes(int max_smem_optin, bool cull);
+}
+namespace rt_prologue {
+cudaError_t run(const rt_object* d_objs, const int32_t* d_kind, const int32_t* d_hot_index, int n_obj,
+                int n_box, int n_sph, RtCold* d_cold, float* d_box_fast, float* d_box_cull, float* d_sph,
+                const RtLightDev* d_lights, int n_lit, const int* lit, float light_reach,
+                unsigned int* d_extent_bits, float* d_obj_lrec, cudaStream_t st);
 }
 namespace rt_strict {
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
@@ -92,6 +99,9 @@ struct HostScene {
     int n_lit = 0;                             // lit lights with records (0: more than 3, or none)
     std::vector<float> sph;                    // (c, r*r)
     std::vector<int32_t> box_obj, sph_obj;
+    std::vector<int32_t> kind, hot_index;      // per original object
+    int lit[3] = {0, 0, 0};                    // indices of the lit lights that have records
+    double light_reach = 1.0;                  // max |light position| (part of the scene extent)
     std::vector<RtCold> cold;
     std::vector<RtLightDev> lights;
     int max_depth = 0;
@@ -113,6 +123,14 @@ struct rt_context {
     DevBuf<uint8_t> d_out;
     DevBuf<RtCounters> d_cnt;
     DevBuf<unsigned long long> d_tile;
+    DevBuf<rt_object> d_objs;                 // device prologue inputs
+    DevBuf<int32_t> d_kind, d_hot;
+    DevBuf<unsigned int> d_extent;
+    int prologue_mode = RT_PROLOGUE_AUTO;
+    bool strict_ready = false;                // d_box_strict holds the current scene
+    std::vector<rt_object> objs_copy;
+    std::vector<rt_light> lights_copy;
+    int depth_copy = 0;
     uint8_t* h_pinned = nullptr;
     size_t h_pinned_cap = 0;
     // uploaded scene
@@ -122,95 +140,21 @@ struct rt_context {
 
 namespace {
 
-bool is_box(const rt_object& o) {   // glsl:749: box != null_box
-    return !(o.box_mins[0] == 0.0f && o.box_mins[1] == 0.0f && o.box_mins[2] == 0.0f &&
-             o.box_maxs[0] == 0.0f && o.box_maxs[1] == 0.0f && o.box_maxs[2] == 0.0f);
-}
-
-// Host prologue: per-object matrices and the hot/cold split.
-int build_host_scene(const rt_scene* scene, HostScene* hs) {
+// Classification (glsl:749, 759) and the hot lists in original order; cheap, always on the host.
+void classify_scene(const rt_scene* scene, HostScene* hs) {
     const int n = scene->objects_count;
-    hs->cold.resize(n > 0 ? n : 0);
-    hs->max_depth = scene->max_depth;
+    hs->kind.assign(n > 0 ? n : 0, RT_KIND_SKIP);
+    hs->hot_index.assign(n > 0 ? n : 0, -1);
+    hs->box_obj.clear(); hs->sph_obj.clear();
     for (int i = 0; i < n; i++) {
-        const rt_object& o = scene->objects[i];
-        RtCold& c = hs->cold[i];
-        memset(&c, 0, sizeof(c));
-        memcpy(c.ambient, o.material.ambient, 16);
-        memcpy(c.diffuse, o.material.diffuse, 16);
-        memcpy(c.specular, o.material.specular, 16);
-        memcpy(c.emissive, o.material.emissive, 16);
-        c.shininess = o.material.shininess;
-        c.reflectivity = o.material.reflectivity;
-        c.transparency = o.material.transparency;
-        c.refraction_index = o.material.refraction_index;
-        memcpy(c.position, o.position, 12);
-        memcpy(c.mins, o.box_mins, 12);
-        memcpy(c.maxs, o.box_maxs, 12);
-        if (is_box(o)) {
-            float l2w[16], w2l[16];
-            rthm::transform(o.position, o.angles, l2w);     // glsl:650
-            rthm::inverse4(l2w, w2l);                       // glsl:652
-            rthm::normal_matrix(l2w, c.nmat);               // glsl:718
-            for (int r = 0; r < 3; r++)
-                for (int k = 0; k < 4; k++) {
-                    c.w2l[4 * r + k] = rthm::at(w2l, r, k);
-                    c.l2w[4 * r + k] = rthm::at(l2w, r, k);
-                }
-            // A slab of zero thickness can never satisfy t_near < t_far (glsl:680): never hit.
-            const bool degenerate = o.box_mins[0] == o.box_maxs[0] || o.box_mins[1] == o.box_maxs[1] ||
-                                    o.box_mins[2] == o.box_maxs[2];
-            // strict record (always built so both kernels see the same object set, modulo degenerate)
-            c.kind = RT_KIND_BOX;
-            c.hot_index = (int32_t)hs->box_obj.size();
-            hs->box_obj.push_back(i);
-            for (int r = 0; r < 3; r++)
-                for (int k = 0; k < 4; k++) hs->box_strict.push_back(c.w2l[4 * r + k]);
-            hs->box_strict.push_back(o.box_mins[0]); hs->box_strict.push_back(o.box_mins[1]);
-            hs->box_strict.push_back(o.box_mins[2]); hs->box_strict.push_back(o.box_maxs[0]);
-            hs->box_strict.push_back(o.box_maxs[1]); hs->box_strict.push_back(o.box_maxs[2]);
-            hs->box_strict.push_back(0.0f); hs->box_strict.push_back(0.0f);
-            // fast record: rows of diag(1/h) * (w2l - centre), h = half extent (double for accuracy).
-            for (int r = 0; r < 3; r++) {
-                const double h = 0.5 * ((double)o.box_maxs[r] - (double)o.box_mins[r]);
-                const double ctr = 0.5 * ((double)o.box_maxs[r] + (double)o.box_mins[r]);
-                if (degenerate) {
-                    // unreachable slab: local'' origin far outside, direction row zero -> always a miss
-                    hs->box_fast.push_back(0.0f); hs->box_fast.push_back(0.0f); hs->box_fast.push_back(0.0f);
-                    hs->box_fast.push_back(4.0f);
-                } else {
-                    const double ih = 1.0 / h;
-                    for (int k = 0; k < 3; k++) hs->box_fast.push_back((float)((double)c.w2l[4 * r + k] * ih));
-                    hs->box_fast.push_back((float)(((double)c.w2l[4 * r + 3] - ctr) * ih));
-                }
-            }
-            // bounding sphere of the box in world space (T*R is rigid: the circumradius is |half extent|);
-            // the radius is stored un-padded here (negative = degenerate) and padded once the scene
-            // extent is known (end of this function)
-            {
-                double ctr[3], r2 = 0.0;
-                for (int r = 0; r < 3; r++) {
-                    ctr[r] = 0.5 * ((double)o.box_maxs[r] + (double)o.box_mins[r]);
-                    const double h = 0.5 * ((double)o.box_maxs[r] - (double)o.box_mins[r]);
-                    r2 += h * h;
-                }
-                for (int r = 0; r < 3; r++)
-                    hs->box_cull.push_back((float)((double)c.l2w[4 * r + 0] * ctr[0] + (double)c.l2w[4 * r + 1] * ctr[1] +
-                                                   (double)c.l2w[4 * r + 2] * ctr[2] + (double)c.l2w[4 * r + 3]));
-                hs->box_cull.push_back(degenerate ? -1.0f : (float)std::sqrt(r2));
-            }
-        } else if (o.sphere_radius != -1.0f) {              // glsl:759
-            c.kind = RT_KIND_SPHERE;
-            c.hot_index = (int32_t)hs->sph_obj.size();
-            hs->sph_obj.push_back(i);
-            hs->sph.push_back(o.position[0]); hs->sph.push_back(o.position[1]); hs->sph.push_back(o.position[2]);
-            hs->sph.push_back(o.sphere_radius * o.sphere_radius);   // glsl:588 radius * radius
-        } else {
-            c.kind = RT_KIND_SKIP;
-            c.hot_index = -1;
-        }
+        const int k = rtpm::object_kind(scene->objects[i]);
+        hs->kind[i] = k;
+        if (k == RT_KIND_BOX) { hs->hot_index[i] = (int32_t)hs->box_obj.size(); hs->box_obj.push_back(i); }
+        else if (k == RT_KIND_SPHERE) { hs->hot_index[i] = (int32_t)hs->sph_obj.size(); hs->sph_obj.push_back(i); }
     }
+    hs->max_depth = scene->max_depth;
     hs->lights.resize(scene->lights_count > 0 ? scene->lights_count : 0);
+    std::vector<int> lit;
     for (int j = 0; j < scene->lights_count; j++) {
         const rt_light& L = scene->lights[j];
         RtLightDev& d = hs->lights[j];
@@ -219,80 +163,58 @@ int build_host_scene(const rt_scene* scene, HostScene* hs) {
         memcpy(d.ambient, L.ambient, 16);
         memcpy(d.diffuse, L.diffuse, 16);
         memcpy(d.specular, L.specular, 16);
-        bool lit = false;   // a light with zero diffuse and specular adds 0 shadowed or not (glsl:830-832)
-        for (int k = 0; k < 4; k++) lit = lit || L.diffuse[k] != 0.0f || L.specular[k] != 0.0f;
-        d.position[3] = lit ? 1.0f : 0.0f;
+        bool is_lit = false;   // a light with zero diffuse and specular adds 0 shadowed or not (glsl:830-832)
+        for (int k = 0; k < 4; k++) is_lit = is_lit || L.diffuse[k] != 0.0f || L.specular[k] != 0.0f;
+        d.position[3] = is_lit ? 1.0f : 0.0f;
+        if (is_lit) lit.push_back(j);
     }
-    // Scene extent E: ray origins (hit points), lights and centres have coordinates up to ~E, so every
-    // difference of two of them carries an absolute FP32 rounding error up to ~E * 2^-23.  The bounding
-    // radii are padded by 5e-4 relative + 2e-6 * E absolute: far more than that rounding and than the
-    // slab test's own, so the bounding-sphere tests never reject a ray the exact test would accept.
-    double extent = 1.0;
-    for (size_t b = 0; b < hs->box_obj.size(); b++) {
-        const float* q = &hs->box_cull[4 * b];
-        extent = std::max(extent, std::sqrt((double)q[0] * q[0] + (double)q[1] * q[1] + (double)q[2] * q[2]) + std::fabs((double)q[3]));
-    }
-    for (size_t j = 0; j < hs->sph_obj.size(); j++) {
-        const float* q = &hs->sph[4 * j];
-        extent = std::max(extent, std::sqrt((double)q[0] * q[0] + (double)q[1] * q[1] + (double)q[2] * q[2]) + std::sqrt(std::fabs((double)q[3])));
-    }
-    for (const RtLightDev& L : hs->lights)
-        extent = std::max(extent, std::sqrt((double)L.position[0] * L.position[0] + (double)L.position[1] * L.position[1] +
-                                            (double)L.position[2] * L.position[2]));
-    const double abs_pad = 2e-6 * extent;
-    std::vector<double> box_rad(hs->box_obj.size());
-    for (size_t b = 0; b < hs->box_obj.size(); b++) {
-        box_rad[b] = hs->box_cull[4 * b + 3];                             // un-padded circumradius, < 0 = degenerate
-        const double rp = box_rad[b] * 1.0005 + abs_pad;
-        hs->box_cull[4 * b + 3] = box_rad[b] < 0.0 ? -1e30f : (float)(rp * rp * (1.0 + 1e-6));
-    }
-    // Per-light records for the shadow rays of large scenes (rt_kernel.cuh: lights_tile).  The shadow
-    // ray of light L starts at p + 0.01 n and runs along L - p (glsl:808-809), i.e. along the line
-    // through L shifted by 0.01 n, |n| = 1 (rigid box transforms, normalised sphere normals): growing
-    // the bounding radius by a further 0.0101 makes "the line through L along d meets the sphere" a
-    // conservative stand-in for "the ray's line meets the primitive".
-    std::vector<int> lit;
-    for (int j = 0; j < (int)hs->lights.size(); j++)
-        if (hs->lights[j].position[3] != 0.0f) lit.push_back(j);
+    // per-light records exist for 1..3 lit lights (one shadow batch); otherwise the generic path runs
     hs->n_lit = (lit.size() >= 1 && lit.size() <= 3) ? (int)lit.size() : 0;
+    for (int s2 = 0; s2 < 3; s2++) hs->lit[s2] = s2 < hs->n_lit ? lit[s2] : 0;
+    hs->light_reach = 1.0;
+    for (const RtLightDev& L : hs->lights) {
+        const float zero[3] = {L.position[0], L.position[1], L.position[2]};
+        hs->light_reach = std::max(hs->light_reach, rtpm::reach(zero, 0.0));
+    }
+}
+
+// Host prologue: per-object matrices and records (rt_prologue_math.h), then the padded bounding records.
+int build_host_scene(const rt_scene* scene, HostScene* hs) {
+    classify_scene(scene, hs);
+    const int n = scene->objects_count;
+    const size_t nb = hs->box_obj.size(), ns = hs->sph_obj.size();
+    hs->cold.resize(n > 0 ? n : 0);
+    hs->box_fast.assign(nb * 12, 0.0f);
+    hs->box_strict.assign(nb * 20, 0.0f);
+    hs->box_cull.assign(nb * 4, 0.0f);
+    hs->sph.assign(ns * 4, 0.0f);
+    for (int i = 0; i < n; i++) {
+        const int k = hs->kind[i], h = hs->hot_index[i];
+        float dummy[20];
+        rtpm::object_records(scene->objects[i], k, h, &hs->cold[i],
+                             k == RT_KIND_BOX ? &hs->box_fast[(size_t)h * 12] : dummy,
+                             k == RT_KIND_BOX ? &hs->box_strict[(size_t)h * 20] : dummy,
+                             k == RT_KIND_BOX ? &hs->box_cull[(size_t)h * 4] : dummy,
+                             k == RT_KIND_SPHERE ? &hs->sph[(size_t)h * 4] : dummy);
+    }
+    double extent = hs->light_reach;
+    for (size_t b = 0; b < nb; b++) extent = std::max(extent, rtpm::reach(&hs->box_cull[4 * b], std::fabs((double)hs->box_cull[4 * b + 3])));
+    for (size_t j = 0; j < ns; j++) extent = std::max(extent, rtpm::reach(&hs->sph[4 * j], std::sqrt(std::fabs((double)hs->sph[4 * j + 3]))));
     if (hs->n_lit > 0) {
-        const int n_hot = (int)(hs->box_obj.size() + hs->sph_obj.size());
+        const int n_hot = (int)(nb + ns);
         const int tiles = (n_hot + 63) / 64;
         hs->obj_lrec.assign((size_t)tiles * hs->n_lit * 64 * 4, 0.0f);
         for (size_t k = 3; k < hs->obj_lrec.size(); k += 4) hs->obj_lrec[k] = 1e30f;   // padding: never passes
         for (int h = 0; h < n_hot; h++) {
-            double c[3], rad;
-            const bool is_b = h < (int)hs->box_obj.size();
-            if (is_b) {
-                for (int r = 0; r < 3; r++) c[r] = hs->box_cull[4 * h + r];
-                if (box_rad[h] < 0.0) continue;                          // degenerate box: never hit
-                rad = box_rad[h];
-            } else {
-                const int j = h - (int)hs->box_obj.size();
-                for (int r = 0; r < 3; r++) c[r] = hs->sph[4 * j + r];
-                rad = std::sqrt((double)hs->sph[4 * j + 3]);
-            }
-            const double rp = rad * 1.0005 + 0.0101 + abs_pad;
-            // The shader's sphere quadratic (glsl:586-591) cancels catastrophically when the ray starts
-            // far from the sphere: its discriminant carries an error of ~2^-22 |o - c|^2 in squared-distance
-            // units and it then reports hits for lines that pass the sphere at some distance.  The record
-            // must let those through as well (the image has to stay identical), hence the E^2 term.
-            const double rp2 = rp * rp + (is_b ? 0.0 : 4e-6 * extent * extent);
-            for (int s2 = 0; s2 < hs->n_lit; s2++) {
-                const RtLightDev& L = hs->lights[lit[s2]];
-                float* rec = &hs->obj_lrec[(((size_t)(h / 64) * hs->n_lit + s2) * 64 + (h % 64)) * 4];
-                double oc2 = 0.0;
-                for (int r = 0; r < 3; r++) {
-                    const double oc = (double)L.position[r] - c[r];
-                    rec[r] = (float)oc;
-                    oc2 += oc * oc;
-                }
-                // rounded toward "pass": the float record must not be larger than the exact value
-                const double qc = oc2 - rp2;
-                rec[3] = (float)(qc - std::fabs(qc) * 1e-6 - 1e-12);
-            }
+            const bool is_b = h < (int)nb;
+            const float* c3 = is_b ? &hs->box_cull[4 * h] : &hs->sph[4 * (h - (int)nb)];
+            const double rad = is_b ? (double)c3[3] : std::sqrt((double)c3[3]);
+            for (int s2 = 0; s2 < hs->n_lit; s2++)
+                rtpm::light_record(c3, rad, is_b, hs->lights[hs->lit[s2]].position, extent,
+                                   &hs->obj_lrec[(((size_t)(h / 64) * hs->n_lit + s2) * 64 + (h % 64)) * 4]);
         }
     }
+    for (size_t b = 0; b < nb; b++) hs->box_cull[4 * b + 3] = rtpm::padded_radius2(hs->box_cull[4 * b + 3], extent);
     return RT_OK;
 }
 
@@ -359,6 +281,7 @@ int rt_destroy(rt_context* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_obj_lrec.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
+    c->d_objs.release(); c->d_kind.release(); c->d_hot.release(); c->d_extent.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -384,12 +307,10 @@ int rt_host_free(void* ptr) {
     return RT_OK;
 }
 
-int rt_upload_scene(rt_context* c, const rt_scene* scene) {
-    if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
-    int rc = validate_scene(scene);
-    if (rc != RT_OK) return rc;
+// Host prologue + upload of every record (all kernels, incl. strict).
+static int upload_host(rt_context* c, const rt_scene* scene) {
     HostScene hs;
-    rc = build_host_scene(scene, &hs);
+    int rc = build_host_scene(scene, &hs);
     if (rc != RT_OK) return rc;
     CU(cudaSetDevice(c->device));
     // The previous frame may still be reading these buffers.
@@ -424,13 +345,89 @@ int rt_upload_scene(rt_context* c, const rt_scene* scene) {
     c->n_lit = hs.n_lit;
     c->max_depth = hs.max_depth;
     c->have_scene = true;
+    c->strict_ready = true;
     return RT_OK;
+}
+
+// Device prologue (rt_prologue.cu): classification on the host, raw objects over PCIe, records built
+// in HBM.  Fast kernel only; a later strict render re-runs the host prologue from the kept copy.
+static int upload_device(rt_context* c, const rt_scene* scene) {
+    HostScene hs;
+    classify_scene(scene, &hs);
+    const size_t n = (size_t)(scene->objects_count > 0 ? scene->objects_count : 0);
+    const size_t nb = hs.box_obj.size(), ns = hs.sph_obj.size();
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(c->d_objs.reserve(n + 1));
+    CU(c->d_kind.reserve(n + 1));
+    CU(c->d_hot.reserve(n + 1));
+    CU(c->d_extent.reserve(1));
+    CU(c->d_box_fast.reserve(nb * 12 + 4));
+    CU(c->d_box_cull.reserve(nb * 4 + 4));
+    CU(c->d_obj_lrec.reserve(((nb + ns + 63) / 64) * (size_t)(hs.n_lit > 0 ? hs.n_lit : 1) * 64 * 4 + 4));
+    CU(c->d_sph.reserve(ns * 4 + 4));
+    CU(c->d_box_obj.reserve(nb + 1));
+    CU(c->d_sph_obj.reserve(ns + 1));
+    CU(c->d_cold.reserve(n + 1));
+    CU(c->d_lights.reserve(hs.lights.size() + 1));
+    auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
+        if (bytes == 0) return cudaSuccess;
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
+    };
+    CU(up(c->d_objs.p, scene->objects, n * sizeof(rt_object)));
+    CU(up(c->d_kind.p, hs.kind.data(), n * 4));
+    CU(up(c->d_hot.p, hs.hot_index.data(), n * 4));
+    CU(up(c->d_box_obj.p, hs.box_obj.data(), nb * 4));
+    CU(up(c->d_sph_obj.p, hs.sph_obj.data(), ns * 4));
+    CU(up(c->d_lights.p, hs.lights.data(), hs.lights.size() * sizeof(RtLightDev)));
+    CU(rt_prologue::run(c->d_objs.p, c->d_kind.p, c->d_hot.p, (int)n, (int)nb, (int)ns, c->d_cold.p, c->d_box_fast.p,
+                        c->d_box_cull.p, c->d_sph.p, c->d_lights.p, hs.n_lit, hs.lit, (float)hs.light_reach,
+                        c->d_extent.p, c->d_obj_lrec.p, c->stream));
+    g_launches += 2 + (hs.n_lit > 0 ? 1 : 0);
+    CU(cudaStreamSynchronize(c->stream));   // the host vectors above go out of scope
+    c->n_box = (int)nb;
+    c->n_sph = (int)ns;
+    c->n_lights = (int)hs.lights.size();
+    c->n_lit = hs.n_lit;
+    c->max_depth = hs.max_depth;
+    c->have_scene = true;
+    c->strict_ready = false;
+    return RT_OK;
+}
+
+int rt_set_prologue(rt_context* c, int mode) {
+    if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
+    if (mode < RT_PROLOGUE_AUTO || mode > RT_PROLOGUE_DEVICE) return fail(RT_ERR_BAD_ARG, "bad prologue mode %d", mode);
+    c->prologue_mode = mode;
+    return RT_OK;
+}
+
+int rt_upload_scene(rt_context* c, const rt_scene* scene) {
+    if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
+    int rc = validate_scene(scene);
+    if (rc != RT_OK) return rc;
+    // keep the scene: a strict render after a device prologue needs the host records
+    c->objs_copy.assign(scene->objects, scene->objects + (scene->objects_count > 0 ? scene->objects_count : 0));
+    c->lights_copy.assign(scene->lights, scene->lights + (scene->lights_count > 0 ? scene->lights_count : 0));
+    c->depth_copy = scene->max_depth;
+    const bool dev = c->prologue_mode == RT_PROLOGUE_DEVICE ||
+                     (c->prologue_mode == RT_PROLOGUE_AUTO && scene->objects_count >= RT_PROLOGUE_DEVICE_MIN_OBJECTS);
+    return dev ? upload_device(c, scene) : upload_host(c, scene);
 }
 
 int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
                        void* out_rgba, int width, int height, const rt_options* opts_in) {
     if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
     if (!c->have_scene) return fail(RT_ERR_BAD_ARG, "no scene uploaded");
+    if (opts_in && opts_in->strict && !c->strict_ready) {
+        // the scene went through the device prologue: the strict kernel wants the host run's records
+        rt_scene sc;
+        sc.objects = c->objs_copy.data(); sc.objects_count = (int32_t)c->objs_copy.size();
+        sc.lights = c->lights_copy.data(); sc.lights_count = (int32_t)c->lights_copy.size();
+        sc.max_depth = c->depth_copy;
+        int rc = upload_host(c, &sc);
+        if (rc != RT_OK) return rc;
+    }
     if (!cameras || n_frames <= 0) return fail(RT_ERR_BAD_ARG, "bad cameras / n_frames");
     if (!out_rgba) return fail(RT_ERR_BAD_ARG, "out_rgba is NULL");
     if (width <= 0 || height <= 0) return fail(RT_ERR_BAD_ARG, "bad image size %dx%d", width, height);

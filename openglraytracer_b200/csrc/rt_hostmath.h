@@ -15,21 +15,28 @@
 #include <math.h>
 #include <string.h>
 
+/* The device prologue (rt_prologue.cu, compiled -fmad=false) runs the same functions on the GPU. */
+#ifdef __CUDACC__
+#define RTHM_FN __host__ __device__ inline
+#else
+#define RTHM_FN inline
+#endif
+
 namespace rthm {
 
-static const float kPi = 3.14159265358f;          /* glsl:13 */
-static const float kDegToRad = kPi / 180.0f;      /* glsl:17 */
+constexpr float kPi = 3.14159265358f;          /* glsl:13 */
+constexpr float kDegToRad = kPi / 180.0f;      /* glsl:17 */
 
-inline float& at(float* m, int r, int c) { return m[4 * c + r]; }
-inline float at(const float* m, int r, int c) { return m[4 * c + r]; }
+RTHM_FN float& at(float* m, int r, int c) { return m[4 * c + r]; }
+RTHM_FN float at(const float* m, int r, int c) { return m[4 * c + r]; }
 
-inline void identity(float* m) {
+RTHM_FN void identity(float* m) {
     for (int i = 0; i < 16; i++) m[i] = 0.0f;
     m[0] = m[5] = m[10] = m[15] = 1.0f;
 }
 
 /* out = a * b; out may not alias a or b */
-inline void mul(const float* a, const float* b, float* out) {
+RTHM_FN void mul(const float* a, const float* b, float* out) {
     for (int c = 0; c < 4; c++)
         for (int r = 0; r < 4; r++) {
             float acc = at(a, r, 0) * at(b, 0, c);
@@ -41,24 +48,24 @@ inline void mul(const float* a, const float* b, float* out) {
 }
 
 /* glsl:444-486 */
-inline void rot_x(float deg, float* m) {
+RTHM_FN void rot_x(float deg, float* m) {
     float c = cosf(kDegToRad * deg), s = sinf(kDegToRad * deg);
     identity(m);
     at(m, 1, 1) = c; at(m, 2, 1) = s; at(m, 1, 2) = -s; at(m, 2, 2) = c;
 }
-inline void rot_y(float deg, float* m) {
+RTHM_FN void rot_y(float deg, float* m) {
     float c = cosf(kDegToRad * deg), s = sinf(kDegToRad * deg);
     identity(m);
     at(m, 0, 0) = c; at(m, 2, 0) = -s; at(m, 0, 2) = s; at(m, 2, 2) = c;
 }
-inline void rot_z(float deg, float* m) {
+RTHM_FN void rot_z(float deg, float* m) {
     float c = cosf(kDegToRad * deg), s = sinf(kDegToRad * deg);
     identity(m);
     at(m, 0, 0) = c; at(m, 1, 0) = s; at(m, 0, 1) = -s; at(m, 1, 1) = c;
 }
 
 /* glsl:492-503: I * Rz(yaw) * Rx(pitch) * Ry(roll), angles = (pitch, yaw, roll) */
-inline void rotation(const float* angles, float* out) {
+RTHM_FN void rotation(const float* angles, float* out) {
     float i4[16], rz[16], rx[16], ry[16], t0[16], t1[16];
     identity(i4);
     rot_z(angles[1], rz); rot_x(angles[0], rx); rot_y(angles[2], ry);
@@ -68,7 +75,7 @@ inline void rotation(const float* angles, float* out) {
 }
 
 /* glsl:529-532: T(position) * R(angles) */
-inline void transform(const float* position, const float* angles, float* out) {
+RTHM_FN void transform(const float* position, const float* angles, float* out) {
     float t[16], r[16];
     identity(t);
     at(t, 0, 3) = position[0]; at(t, 1, 3) = position[1]; at(t, 2, 3) = position[2]; at(t, 3, 3) = 1.0f;
@@ -77,7 +84,7 @@ inline void transform(const float* position, const float* angles, float* out) {
 }
 
 /* inverse(mat4): adjugate from 2x2 sub-determinants, times 1/det */
-inline void inverse4(const float* m, float* out) {
+RTHM_FN void inverse4(const float* m, float* out) {
 #define A(i, j) at(m, i, j)
     float s0 = A(0,0) * A(1,1) - A(1,0) * A(0,1);
     float s1 = A(0,0) * A(1,2) - A(1,0) * A(0,2);
@@ -113,7 +120,7 @@ inline void inverse4(const float* m, float* out) {
 }
 
 /* transpose(inverse(mat3(m))) as 9 floats, column-major n[3*c + r] (glsl:718) */
-inline void normal_matrix(const float* m, float* n) {
+RTHM_FN void normal_matrix(const float* m, float* n) {
 #define A(i, j) at(m, i, j)
     float k00 = A(1,1) * A(2,2) - A(1,2) * A(2,1);
     float k01 = A(1,2) * A(2,0) - A(1,0) * A(2,2);
@@ -137,7 +144,7 @@ inline void normal_matrix(const float* m, float* n) {
 }
 
 /* glsl:411-426 */
-inline void projection(float v_fov, float aspect, float near_plane, float far_plane, float* m) {
+RTHM_FN void projection(float v_fov, float aspect, float near_plane, float far_plane, float* m) {
     float q = 1.0f / tanf(kDegToRad * 0.5f * v_fov);
     float A = q / aspect;
     float B = (near_plane + far_plane) / (near_plane - far_plane);
@@ -151,7 +158,7 @@ inline void projection(float v_fov, float aspect, float near_plane, float far_pl
 }
 
 /* glsl:538-545: inverse(T*R * Rx(90)) */
-inline void view(const float* position, const float* angles, float* out) {
+RTHM_FN void view(const float* position, const float* angles, float* out) {
     float tr[16], flip[16], prod[16];
     transform(position, angles, tr);
     rot_x(90.0f, flip);
@@ -160,7 +167,7 @@ inline void view(const float* position, const float* angles, float* out) {
 }
 
 /* glsl:383: inverse(proj * view) */
-inline void inverse_proj_view(const float* position, const float* angles, float v_fov, float aspect,
+RTHM_FN void inverse_proj_view(const float* position, const float* angles, float v_fov, float aspect,
                               float near_plane, float far_plane, float* out) {
     float p[16], v[16], pv[16];
     projection(v_fov, aspect, near_plane, far_plane, p);

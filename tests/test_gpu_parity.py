@@ -198,6 +198,52 @@ def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
     assert np.array_equal(canvas, on)
 
 
+def test_large_scene_kernel_with_spp_and_batch(tracer):
+    """The large-scene kernel (three primary rays per lane, bounding tests, light records) with jittered
+    samples and several cameras in one launch, held to the oracle and to the single-frame call."""
+    sc = rt.scaled_scene(200, max_depth=1)
+    cams = rt.turntable_cameras(3)
+    w, h = 100, 52                              # not a multiple of the 24-pixel work item
+    batch = tracer.render(sc, cams, w, h, spp=4)
+    assert batch.shape == (3, h, w, 4)
+    for k in range(3):
+        assert np.array_equal(batch[k], tracer.render(sc, cams[k], w, h, spp=4))
+    _check(batch[1], ob.render(sc, cams[1], w, h, spp=4), "scaled 200 spp4 batch frame 1", need_edges=False)
+    assert np.array_equal(batch, tracer.render(sc, cams, w, h, spp=4, no_cull=1))
+    for (ww, hh) in [(1, 1), (23, 5), (25, 4), (49, 3)]:
+        img = tracer.render(sc, cams[0], ww, hh)
+        rep = compare(img, ob.render(sc, cams[0], ww, hh))
+        assert rep["over_1"] <= max(1, int(0.03 * ww * hh)), rep
+
+
+def test_device_prologue_matches_host_prologue_and_oracle():
+    """the per-object prologue (glsl:650-652, 718 hoisted) as device kernels.  Same
+    functions as the host run; only sinf / cosf differ (CUDA vs glibc), so frames agree with the host
+    prologue's on all but a few hit-decision pixels and hold the same parity against the oracle."""
+    with rt.Raytracer(0) as dev, rt.Raytracer(0) as host:
+        dev.set_prologue("device")
+        host.set_prologue("host")
+        for sc, cam, w, h in [(rt.builtin_scene(2.5, 3), rt.builtin_camera(2.5), 320, 180),
+                              (rt.scaled_scene(200, max_depth=1), rt.builtin_camera(0.0), 256, 144),
+                              (rt.scaled_scene(4096, max_depth=0), rt.builtin_camera(0.0), 256, 144)]:
+            before = rt.kernel_launch_count()
+            a = dev.render(sc, cam, w, h)
+            assert rt.kernel_launch_count() >= before + 3          # prologue kernels + render kernel
+            b = host.render(sc, cam, w, h)
+            same = (a == b).all(axis=2).mean()
+            assert same >= 0.999, same
+            _check(a, ob.render(sc, cam, w, h), "device prologue %d objects" % sc.objects_count, need_edges=False)
+            # bands and the bounding-test switch stay byte-identical under the device prologue too
+            assert np.array_equal(a, dev.render(sc, cam, w, h, no_cull=1))
+            top = dev.render(sc, cam, w, h, y0=0, y1=50, band_only=True)
+            assert np.array_equal(top, a[:50])
+            # a strict render after a device prologue falls back to the host records (op-for-op parity)
+            st = dev.render(sc, cam, w, h, strict=True)
+            assert np.array_equal(st, host.render(sc, cam, w, h, strict=True))
+        with pytest.raises(KeyError):
+            dev.set_prologue("gpu")
+
+
 def _far_scene(cube_half):
     base = rt.builtin_scene(0.0, 1)
     n = 64

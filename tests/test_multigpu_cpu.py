@@ -11,7 +11,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from openglraytracer_b200.multigpu import frame_block, gather_bands, row_band
+from openglraytracer_b200.multigpu import frame_block, frame_stride_set, gather_bands, row_band
 
 
 def test_row_bands_partition_rows_exactly():
@@ -24,6 +24,8 @@ def test_row_bands_partition_rows_exactly():
             assert max(rows) - min(rows) <= 1
     assert row_band(3, 8, 2160) == (810, 1080)       # 270-row bands at 4K / 8 GPUs
     assert [frame_block(r, 8, 256) for r in (0, 7)] == [(0, 32), (224, 256)]
+    assert sorted(k for r in range(8) for k in frame_stride_set(r, 8, 250)) == list(range(250))
+    assert frame_stride_set(3, 8, 256)[:3] == [3, 11, 19]
 
 
 def _free_port():
