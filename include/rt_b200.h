@@ -129,9 +129,16 @@ typedef struct rt_options {
     int32_t async;            /* 1 = do not synchronise (device output only); pair with rt_synchronize() */
     void* stream;             /* cudaStream_t to launch on; NULL = the context's own stream */
     rt_stats* stats;          /* optional counters/timings */
+    int32_t host_store;       /* page-locked host out_rgba: RT_HOST_STORE_AUTO (0) lets the kernel store the frame
+                               * straight into it over PCIe when the frame is heavy enough to hide the traffic,
+                               * _ALWAYS (1), _NEVER (2: device frame + device->host copy) */
     int32_t no_cull;          /* A/B switches, same image: bit 0 = large scenes run every slab test (no bounding-sphere
                                * test first); bit 1 = shadow rays do not use the per-light records */
 } rt_options;
+
+#define RT_HOST_STORE_AUTO   0
+#define RT_HOST_STORE_ALWAYS 1
+#define RT_HOST_STORE_NEVER  2
 
 typedef struct rt_context rt_context;
 

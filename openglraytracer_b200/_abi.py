@@ -62,7 +62,7 @@ class Options(C.Structure):
     _fields_ = [("spp", C.c_int32), ("seed", C.c_uint32), ("y0", C.c_int32), ("y1", C.c_int32),
                 ("out_is_device", C.c_int32), ("out_band_only", C.c_int32), ("device", C.c_int32),
                 ("strict", C.c_int32), ("async_", C.c_int32), ("stream", C.c_void_p),
-                ("stats", C.POINTER(Stats)), ("no_cull", C.c_int32)]
+                ("stats", C.POINTER(Stats)), ("host_store", C.c_int32), ("no_cull", C.c_int32)]
 
 
 # Every symbol include/rt_b200.h declares (tests check the library exports all of them).

@@ -163,7 +163,7 @@ class Raytracer:
         check(self._lib.rt_synchronize(self._ctx), "rt_synchronize")
 
     @staticmethod
-    def _options(spp, seed, y0, y1, strict, out_is_device, band_only, async_, stream, stats, no_cull=False):
+    def _options(spp, seed, y0, y1, strict, out_is_device, band_only, async_, stream, stats, no_cull=False, host_store=0):
         o = Options()
         _abi.lib().rt_options_default(C.byref(o))
         o.spp, o.seed, o.y0, o.y1 = int(spp), int(seed), int(y0), int(y1)
@@ -171,6 +171,7 @@ class Raytracer:
         o.async_ = int(async_)
         o.stream = stream
         o.no_cull = int(no_cull)
+        o.host_store = int(host_store)
         if stats is not None:
             o.stats = C.pointer(stats)
         return o
@@ -182,7 +183,7 @@ class Raytracer:
 
     def render(self, scene, camera_uniforms, width, height, *, spp=1, seed=0x5EED0001, y0=0, y1=0,
                strict=False, out=None, out_device_ptr=None, band_only=False, async_=False, stream=None,
-               want_stats=False, no_cull=False):
+               want_stats=False, no_cull=False, host_store=0):
         """Render one frame (camera_uniforms: Camera) or a batch (ctypes array of Camera).
 
         scene=None re-uses the last uploaded scene.  Host output: numpy uint8
@@ -205,7 +206,7 @@ class Raytracer:
                 out = np.empty((n, rows, width, 4) if batch else (rows, width, 4), np.uint8)
             if out.nbytes != n * rows * width * 4 or not out.flags["C_CONTIGUOUS"] or out.dtype != np.uint8:
                 raise ValueError("out must be a C-contiguous uint8 array of %d bytes" % (n * rows * width * 4))
-            opts = self._options(spp, seed, y0, y1, strict, 0, band_only, False, stream, stats, no_cull)
+            opts = self._options(spp, seed, y0, y1, strict, 0, band_only, False, stream, stats, no_cull, host_store)
             target = C.c_void_p(out.ctypes.data)
             result = out
         if scene is not None:

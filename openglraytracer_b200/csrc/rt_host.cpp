@@ -488,8 +488,23 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin, false)
                                         : rt_fast::resident_limit_bytes(c->max_smem_optin, P.cull != 0)) ? 1 : 0;
 
-    if (o.out_is_device) {
-        P.out = (uint8_t*)out_rgba;
+    // Page-locked host output (rt_host_alloc): the kernel's 16-byte framebuffer stores can go straight
+    // to host memory over PCIe (posted writes, overlapped with the rendering) instead of a device frame
+    // plus a device->host copy after the kernel.
+    uint8_t* host_mapped = nullptr;
+    if (!o.out_is_device && o.host_store != RT_HOST_STORE_NEVER) {
+        cudaPointerAttributes pa;
+        if (cudaPointerGetAttributes(&pa, out_rgba) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer) {
+            // auto: worth it when the frame takes clearly longer to render than to push over PCIe
+            // (bounce depth >= 1 or many objects or several samples); a depth-0 built-in frame is faster with the copy
+            const bool heavy = c->max_depth >= 1 || c->n_box + c->n_sph >= 48 || spp > 1;
+            if (o.host_store == RT_HOST_STORE_ALWAYS || heavy) host_mapped = (uint8_t*)pa.devicePointer;
+        } else {
+            (void)cudaGetLastError();   // pageable memory: not an error
+        }
+    }
+    if (o.out_is_device || host_mapped) {
+        P.out = o.out_is_device ? (uint8_t*)out_rgba : host_mapped;
         P.frame_stride = band_only ? (long long)frame_bytes_band : (long long)frame_bytes_full;
         P.out_row0 = band_only ? y0 : 0;
     } else {
@@ -516,7 +531,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         g_launches++;
     }
 
-    if (!o.out_is_device) {
+    if (!o.out_is_device && !host_mapped) {
         uint8_t* dst = (uint8_t*)out_rgba;
         for (int k = 0; k < n_frames; k++) {
             uint8_t* d = band_only ? dst + (size_t)k * frame_bytes_band

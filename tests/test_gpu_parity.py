@@ -146,9 +146,18 @@ def test_device_output_and_pinned_host(tracer):
     tracer.render(sc, cam, w, h, out_device_ptr=dev.data_ptr())
     assert np.array_equal(dev.cpu().numpy(), ref)
     pin = rt.PinnedImage((h, w, 4))
-    tracer.render(sc, cam, w, h, out=pin.array)
-    assert np.array_equal(pin.array, ref)
+    # page-locked host frame: kernel stores straight into it over PCIe (1), device frame + copy (2), auto (0)
+    for mode in (0, 1, 2):
+        pin.array[:] = 7
+        tracer.render(sc, cam, w, h, out=pin.array, host_store=mode)
+        assert np.array_equal(pin.array, ref)
+    pin.array[:] = 7
+    tracer.render(sc, cam, w, h, out=pin.array, host_store=1, y0=16, y1=60)      # a band, in place
+    assert np.array_equal(pin.array[16:60], ref[16:60]) and (pin.array[:16] == 7).all() and (pin.array[60:] == 7).all()
     pin.free()
+    pageable = np.full((h, w, 4), 7, np.uint8)
+    tracer.render(sc, cam, w, h, out=pageable, host_store=1)                       # not page-locked: falls back to the copy
+    assert np.array_equal(pageable, ref)
 
 
 @pytest.mark.parametrize("n,depth", [(64, 2), (1024, 1), (4096, 1)])
