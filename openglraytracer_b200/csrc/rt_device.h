@@ -33,8 +33,9 @@ struct RtCold {
     float w2l[12];      /* world->local rows: row i = (m[0][i], m[1][i], m[2][i], m[3][i]) of inverse(T*R), glsl:652 */
     float l2w[12];      /* local->world rows, glsl:650 */
     float nmat[9];      /* transpose(inverse(mat3(l2w))), column-major c[col][row], glsl:718 */
-    float mins[3];
-    float maxs[3];
+    float inv_ior;      /* 1 / refraction_index (glsl:1013), IEEE */
+    float ior_back;     /* 1 / inv_ior (glsl:1017-1020: the ratio is inverted again for a ray leaving the object) */
+    float unused_[4];
     int32_t kind;
     int32_t hot_index;  /* index in the box / sphere hot list */
     /* material (glsl:56-69) */

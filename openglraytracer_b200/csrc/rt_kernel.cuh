@@ -84,7 +84,15 @@ __device__ __forceinline__ float fpow(float x, float y) { return powf(x, y); }
 // outside the hot loop but were ~40 % of the small-scene kernel's code size (instruction cache).
 __device__ __forceinline__ V3 normalize3(V3 v) { float r = rsqrtf(dot3(v, v)); return mk(v.x * r, v.y * r, v.z * r); }
 __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
-__device__ __forceinline__ float fpow(float x, float y) { return (y == 0.0f) ? 1.0f : exp2f(y * log2f(x)); }
+// pow (glsl:832) as ex2.approx(y * lg2.approx(x)): two MUFU ops.  |error of lg2.approx| <= 2^-21.4 absolute on
+// [0.5, 2), so the relative error of the result is about y * 4e-7 (shininess 10: 3e-6, against half an
+// RGBA8 LSB = 2e-3); x = 0 gives ex2(-inf) = 0 and y = 0 gives 1 like powf.
+__device__ __forceinline__ float fpow(float x, float y) {
+    float l, r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(x));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(y * l));
+    return (y == 0.0f) ? 1.0f : r;
+}
 #endif
 __device__ __forceinline__ V3 reflect3(V3 I, V3 N) { float d2 = 2.0f * dot3(N, I); return I - d2 * N; }
 __device__ __forceinline__ V3 refract3(V3 I, V3 N, float eta) {
@@ -177,7 +185,11 @@ struct SphO { V3 oc; float qc; };      // per (origin, sphere)
 __device__ __forceinline__ RayQ ray_q(V3 d) {
     RayQ q;
     q.qa = __fmaf_rn(d.x, d.x, __fmaf_rn(d.y, d.y, __fmul_rn(d.z, d.z)));
+#if RT_STRICT
     q.iqa = 1.0f / q.qa;
+#else
+    q.iqa = rcp_approx(q.qa);       // 1 ulp in the sphere's t, like the box test's reciprocals
+#endif
     return q;
 }
 
@@ -332,7 +344,7 @@ __device__ __forceinline__ void tile_drain(WarpCtx& w, int t, int n_tiles) {
 //   ANYHIT : shadow semantics (glsl:816: in shadow iff ANY object is hit at 0 < t < 1).
 // Most tests miss, so the accept logic sits behind one warp vote per box.
 // -------------------------------------------------------------------------
-template <int R, bool ANYHIT, bool SHARED, bool COUNT>
+template <int R, bool ANYHIT, bool SHARED, bool COUNT, bool VOTE = true>
 __device__ __forceinline__ void boxes_tile(const float4* __restrict__ recs, int n, int base,
                                            const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
                                            float (&best)[kShadowBatch], int (&bidx)[kShadowBatch],
@@ -354,7 +366,9 @@ __device__ __forceinline__ void boxes_tile(const float4* __restrict__ recs, int 
             box_slabs(rec, so, d[r], tn[r], tf[r], s, ld);
             cand = cand || !box_reject(tn[r], tf[r]);
         }
-        if (__any_sync(kFull, cand)) {
+        // VOTE = false (a handful of large objects, e.g. the built-in scene: most tests hit): the accept
+        // logic runs straight-line, the vote and branch would only add to it
+        if (!VOTE || __any_sync(kFull, cand)) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 const float t = box_pick(tn[r], tf[r]);
@@ -791,7 +805,7 @@ template <int R, bool ANYHIT, bool SHARED, bool COUNT>
 __device__ __forceinline__ void all_objects(const RtParams& P, const WarpCtx& w,
                                             const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
                                             float (&best)[kShadowBatch], int (&bidx)[kShadowBatch], RtCounters& cnt) {
-    boxes_tile<R, ANYHIT, SHARED, COUNT>(smem_f4 + w.box_off4, P.n_box, 0, o, d, best, bidx, cnt.box_tests);
+    boxes_tile<R, ANYHIT, SHARED, COUNT, false>(smem_f4 + w.box_off4, P.n_box, 0, o, d, best, bidx, cnt.box_tests);
     spheres_tile<R, ANYHIT, SHARED, COUNT, false>(P, smem_f4 + w.sph_off4, P.n_sph, 0, o, d, best, bidx, cnt);
 }
 
@@ -1216,8 +1230,9 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             // PHASES 2-3: each child ray is pushed with its product weight
             if (refracted) {                                                                        // glsl:1010-1027
                 const V3 ro = h.p - h.n * 0.001f;
-                float ratio = 1.0f / mat->refraction_index;
-                if (h.inside) ratio = 1.0f / ratio;
+                // glsl:1013-1020: ratio = 1 / ior, inverted again when leaving the object; both IEEE
+                // quotients are per-object constants, built by the prologue
+                const float ratio = h.inside ? mat->ior_back : mat->inv_ior;
                 const V3 rdv = refract3(d[0], h.n, ratio);
                 stk[sp][0] = ro.x; stk[sp][1] = ro.y; stk[sp][2] = ro.z;
                 stk[sp][3] = rdv.x; stk[sp][4] = rdv.y; stk[sp][5] = rdv.z;

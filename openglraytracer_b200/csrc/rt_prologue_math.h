@@ -42,7 +42,10 @@ RTHM_FN void object_records(const rt_object& o, int kind, int hot_index, RtCold*
     c.reflectivity = o.material.reflectivity;
     c.transparency = o.material.transparency;
     c.refraction_index = o.material.refraction_index;
-    for (int k = 0; k < 3; k++) { c.position[k] = o.position[k]; c.mins[k] = o.box_mins[k]; c.maxs[k] = o.box_maxs[k]; }
+    for (int k = 0; k < 3; k++) c.position[k] = o.position[k];
+    c.inv_ior = 1.0f / o.material.refraction_index;
+    c.ior_back = 1.0f / c.inv_ior;
+    for (int k = 0; k < 4; k++) c.unused_[k] = 0.0f;
     c.kind = kind;
     c.hot_index = hot_index;
     for (int k = 0; k < 12; k++) { c.w2l[k] = 0.0f; c.l2w[k] = 0.0f; }
