@@ -92,6 +92,9 @@ struct RtParams {
     int32_t tiles_x, tiles_y;   /* 8x4-pixel warp tiles covering width x (y1-y0) */
     int32_t resident;           /* 1: whole hot scene staged in shared memory once per CTA */
     int32_t n_lit;              /* lit lights with per-light records (1..3), 0 = shadow rays take the generic path */
+    int32_t n_lit_batch;        /* fast kernel: number of lit lights if <= 3 (one shadow batch, lit[] valid), else -1 */
+    int32_t lit[3];             /* indices of the lit lights */
+    float amb_sum[4];           /* sum of the lights' ambient terms, in light order (glsl:801) */
     int32_t cull;               /* 1: large-scene kernels run the slab test behind the bounding-sphere test */
 };
 

@@ -102,6 +102,8 @@ struct HostScene {
     std::vector<int32_t> kind, hot_index;      // per original object
     int lit[3] = {0, 0, 0};                    // indices of the lit lights that have records
     double light_reach = 1.0;                  // max |light position| (part of the scene extent)
+    int n_lit_total = 0;                       // lit lights, any number
+    float amb_sum[4] = {0, 0, 0, 0};           // sum of the lights' ambient terms in light order (glsl:801)
     std::vector<RtCold> cold;
     std::vector<RtLightDev> lights;
     int max_depth = 0;
@@ -136,6 +138,8 @@ struct rt_context {
     // uploaded scene
     bool have_scene = false;
     int n_box = 0, n_sph = 0, n_lights = 0, max_depth = 0, n_lit = 0;
+    int n_lit_total = 0, lit[3] = {0, 0, 0};
+    float amb_sum[4] = {0, 0, 0, 0};
 };
 
 namespace {
@@ -170,6 +174,12 @@ void classify_scene(const rt_scene* scene, HostScene* hs) {
     }
     // per-light records exist for 1..3 lit lights (one shadow batch); otherwise the generic path runs
     hs->n_lit = (lit.size() >= 1 && lit.size() <= 3) ? (int)lit.size() : 0;
+    hs->n_lit_total = (int)lit.size();
+    for (int k = 0; k < 4; k++) {
+        float acc = 0.0f;
+        for (const RtLightDev& L : hs->lights) acc = acc + L.ambient[k];
+        hs->amb_sum[k] = acc;
+    }
     for (int s2 = 0; s2 < 3; s2++) hs->lit[s2] = s2 < hs->n_lit ? lit[s2] : 0;
     hs->light_reach = 1.0;
     for (const RtLightDev& L : hs->lights) {
@@ -343,6 +353,8 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     c->n_sph = (int)hs.sph_obj.size();
     c->n_lights = (int)hs.lights.size();
     c->n_lit = hs.n_lit;
+    c->n_lit_total = hs.n_lit_total;
+    memcpy(c->lit, hs.lit, sizeof(c->lit)); memcpy(c->amb_sum, hs.amb_sum, sizeof(c->amb_sum));
     c->max_depth = hs.max_depth;
     c->have_scene = true;
     c->strict_ready = true;
@@ -389,6 +401,8 @@ static int upload_device(rt_context* c, const rt_scene* scene) {
     c->n_sph = (int)ns;
     c->n_lights = (int)hs.lights.size();
     c->n_lit = hs.n_lit;
+    c->n_lit_total = hs.n_lit_total;
+    memcpy(c->lit, hs.lit, sizeof(c->lit)); memcpy(c->amb_sum, hs.amb_sum, sizeof(c->amb_sum));
     c->max_depth = hs.max_depth;
     c->have_scene = true;
     c->strict_ready = false;
@@ -483,6 +497,8 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     // only the 16-byte bounding-sphere records are staged / streamed (rt_kernel.cuh: boxes_tile_cull).
     P.cull = (!o.strict && !(o.no_cull & 1)) ? 1 : 0;
     P.n_lit = (P.cull && !(o.no_cull & 2)) ? c->n_lit : 0;
+    P.n_lit_batch = c->n_lit_total <= 3 ? c->n_lit_total : -1;
+    memcpy(P.lit, c->lit, sizeof(P.lit)); memcpy(P.amb_sum, c->amb_sum, sizeof(P.amb_sum));
     size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : (P.cull ? 1 : RT_BOX_F4_FAST)) + P.n_sph) * 16;
     if (P.n_lit > 0) hot_bytes += (size_t)((P.n_box + P.n_sph + 63) / 64) * P.n_lit * 64 * 16;
     P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin, false)

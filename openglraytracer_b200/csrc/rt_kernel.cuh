@@ -1163,27 +1163,45 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
         if (COUNT && hit && !shade) { cnt.rays += P.n_lights; cnt.shadow_rays += P.n_lights; cnt.pad += P.n_lights; }
         if (shade) view = normalize3(-d[0]);                        // glsl:827 normalize(-r.dir)
         if (__any_sync(kFull, shade)) {
-            // ambient term of every light, in light order (glsl:801)
-            for (int l = 0; l < P.n_lights; ++l) {
+            // P.n_lit_batch >= 0 (fast kernel, at most 3 lit lights): the host prologue has summed the
+            // lights' ambient terms (glsl:801) and listed the lit lights, so there is one shadow batch and
+            // no per-node loop over the light list.  Otherwise (strict kernel, > 3 lit lights): the loops.
+            const bool one_batch = !RT_STRICT && P.n_lit_batch >= 0;
+            if (one_batch) {
                 if (shade) {
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) amb[k] += P.lights[l].ambient[k] * mat->ambient[k];
-                    if (COUNT) { cnt.rays++; cnt.shadow_rays++; }
+                    for (int k = 0; k < 4; ++k) amb[k] = P.amb_sum[k] * mat->ambient[k];
+                    if (COUNT) { cnt.rays += P.n_lights; cnt.shadow_rays += P.n_lights; cnt.pad += P.n_lights - P.n_lit_batch; }
+                }
+            } else {
+                // ambient term of every light, in light order (glsl:801)
+                for (int l = 0; l < P.n_lights; ++l) {
+                    if (shade) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) amb[k] += P.lights[l].ambient[k] * mat->ambient[k];
+                        if (COUNT) { cnt.rays++; cnt.shadow_rays++; }
+                    }
                 }
             }
             // shadow rays toward the lit lights, kShadowBatch at a time (the light list is warp-uniform)
             int l = 0;
-            while (l < P.n_lights) {
+            while (one_batch ? l == 0 : l < P.n_lights) {
                 int li[kShadowBatch];
                 int n_slots = 0;
-                while (l < P.n_lights && n_slots < kShadowBatch) {
-                    if (P.lights[l].position[3] != 0.0f) {
-                        if (n_slots == 0) li[0] = l; else if (n_slots == 1) li[1] = l; else li[2] = l;
-                        ++n_slots;
-                    } else if (COUNT && shade) {
-                        cnt.pad++;
+                if (one_batch) {
+                    li[0] = P.lit[0]; li[1] = P.lit[1]; li[2] = P.lit[2];
+                    n_slots = P.n_lit_batch;
+                    l = P.n_lights;
+                } else {
+                    while (l < P.n_lights && n_slots < kShadowBatch) {
+                        if (P.lights[l].position[3] != 0.0f) {
+                            if (n_slots == 0) li[0] = l; else if (n_slots == 1) li[1] = l; else li[2] = l;
+                            ++n_slots;
+                        } else if (COUNT && shade) {
+                            cnt.pad++;
+                        }
+                        ++l;
                     }
-                    ++l;
                 }
                 if (n_slots == 0) break;
                 V3 so = mk(0.0f, 0.0f, 0.0f), sd[kShadowBatch];
