@@ -113,6 +113,7 @@ typedef struct rt_stats {
     float total_ms;           /* CUDA-event time incl. uploads and the D2H copy */
     uint64_t cull_tests;      /* bounding-sphere / discriminant tests executed for live rays (large scenes) */
     uint64_t warp_iters;      /* bounce-loop iterations summed over warps; nodes/(32*warp_iters) = lane use */
+    uint64_t packet_tests;    /* (object, cone) tests of the packet loops, one object per lane (large scenes) */
 } rt_stats;
 
 /* Extended options; zero-initialise then override (rt_options_default()). The
@@ -133,7 +134,8 @@ typedef struct rt_options {
                                * straight into it over PCIe when the frame is heavy enough to hide the traffic,
                                * _ALWAYS (1), _NEVER (2: device frame + device->host copy) */
     int32_t no_cull;          /* A/B switches, same image: bit 0 = large scenes run every slab test (no bounding-sphere
-                               * test first); bit 1 = shadow rays do not use the per-light records */
+                               * test first); bit 1 = shadow rays do not use the per-light records; bit 2 = no packet
+                               * (cone) tests, every ray meets every bounding sphere itself */
 } rt_options;
 
 #define RT_HOST_STORE_AUTO   0

@@ -28,6 +28,9 @@
 #define RT_BOX_F4_FAST   3   /* rows of the recentred, 1/half-extent-scaled world->local map */
 #define RT_BOX_F4_STRICT 5   /* world->local rows (3) + (mins.xyz, maxs.x) + (maxs.y, maxs.z, 0, 0) */
 
+/* from this many hot objects the large-scene kernels put the packet (cone) tests in front of the per-ray loops */
+#define RT_PACKET_MIN_OBJECTS 96
+
 /* Cold record: 64 words. */
 struct RtCold {
     float w2l[12];      /* world->local rows: row i = (m[0][i], m[1][i], m[2][i], m[3][i]) of inverse(T*R), glsl:652 */
@@ -68,6 +71,7 @@ struct RtCounters {
     unsigned long long rays, nodes, hit_nodes, shadow_rays, box_tests, sphere_tests, red_pixels, pad;   /* pad = shadow rays resolved without traversal */
     unsigned long long cull_tests;   /* bounding-sphere tests executed for live rays (large-scene kernels) */
     unsigned long long warp_iters;   /* bounce-loop iterations summed over warps: nodes / (32 * warp_iters) = lane utilisation */
+    unsigned long long packet_tests; /* (object, cone) tests of the packet loops, one per lane (large-scene kernels) */
 };
 
 struct RtParams {
@@ -96,6 +100,8 @@ struct RtParams {
     int32_t lit[3];             /* indices of the lit lights */
     float amb_sum[4];           /* sum of the lights' ambient terms, in light order (glsl:801) */
     int32_t cull;               /* 1: large-scene kernels run the slab test behind the bounding-sphere test */
+    int32_t packet;             /* 1: coherent packets (primary rays, shadow rays per light) run the cone test first */
+    const float* extent;        /* scene extent E (max |centre| + radius over objects and lights), written by the prologue */
 };
 
 #endif

@@ -102,6 +102,7 @@ struct HostScene {
     std::vector<int32_t> kind, hot_index;      // per original object
     int lit[3] = {0, 0, 0};                    // indices of the lit lights that have records
     double light_reach = 1.0;                  // max |light position| (part of the scene extent)
+    float extent_f = 1.0f;                     // scene extent E, rounded up
     int n_lit_total = 0;                       // lit lights, any number
     float amb_sum[4] = {0, 0, 0, 0};           // sum of the lights' ambient terms in light order (glsl:801)
     std::vector<RtCold> cold;
@@ -225,6 +226,7 @@ int build_host_scene(const rt_scene* scene, HostScene* hs) {
         }
     }
     for (size_t b = 0; b < nb; b++) hs->box_cull[4 * b + 3] = rtpm::padded_radius2(hs->box_cull[4 * b + 3], extent);
+    hs->extent_f = (float)(extent * 1.000001);      // the kernel's packet tests scale their pads with it
     return RT_OK;
 }
 
@@ -334,10 +336,12 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     CU(c->d_sph_obj.reserve(hs.sph_obj.size() + 1));
     CU(c->d_cold.reserve(hs.cold.size() + 1));
     CU(c->d_lights.reserve(hs.lights.size() + 1));
+    CU(c->d_extent.reserve(1));
     auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
         if (bytes == 0) return cudaSuccess;
         return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
     };
+    CU(up(c->d_extent.p, &hs.extent_f, 4));
     CU(up(c->d_box_fast.p, hs.box_fast.data(), hs.box_fast.size() * 4));
     CU(up(c->d_box_strict.p, hs.box_strict.data(), hs.box_strict.size() * 4));
     CU(up(c->d_box_cull.p, hs.box_cull.data(), hs.box_cull.size() * 4));
@@ -496,7 +500,11 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     // Large scenes (fast kernel): the slab test runs behind a conservative bounding-sphere test, and
     // only the 16-byte bounding-sphere records are staged / streamed (rt_kernel.cuh: boxes_tile_cull).
     P.cull = (!o.strict && !(o.no_cull & 1)) ? 1 : 0;
-    P.n_lit = (P.cull && !(o.no_cull & 2)) ? c->n_lit : 0;
+    // Packet (cone) tests in front of the per-ray bounding tests; the per-light records are then only a
+    // fallback for incoherent packets and are left out (they would halve the resident capacity).
+    P.packet = (P.cull && !(o.no_cull & 4) && c->n_box + c->n_sph >= RT_PACKET_MIN_OBJECTS) ? 1 : 0;
+    P.extent = reinterpret_cast<const float*>(c->d_extent.p);
+    P.n_lit = (P.cull && !P.packet && !(o.no_cull & 2)) ? c->n_lit : 0;
     P.n_lit_batch = c->n_lit_total <= 3 ? c->n_lit_total : -1;
     memcpy(P.lit, c->lit, sizeof(P.lit)); memcpy(P.amb_sum, c->amb_sum, sizeof(P.amb_sum));
     size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : (P.cull ? 1 : RT_BOX_F4_FAST)) + P.n_sph) * 16;
@@ -568,7 +576,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         s->rays = hc.rays; s->nodes = hc.nodes; s->hit_nodes = hc.hit_nodes; s->shadow_rays = hc.shadow_rays;
         s->box_tests = hc.box_tests; s->sphere_tests = hc.sphere_tests; s->red_pixels = hc.red_pixels;
         s->rays_not_traversed = hc.pad;
-        s->cull_tests = hc.cull_tests; s->warp_iters = hc.warp_iters;
+        s->cull_tests = hc.cull_tests; s->warp_iters = hc.warp_iters; s->packet_tests = hc.packet_tests;
         CU(cudaEventElapsedTime(&s->kernel_ms, c->ev[0], c->ev[1]));
         CU(cudaEventElapsedTime(&s->total_ms, c->ev[2], c->ev[3]));
     }

@@ -252,13 +252,15 @@ constexpr int kTileBytes = kTileBox * RT_BOX_F4 * 16;
 constexpr int kTileSph = kTileBytes / 16;                      // spheres per tile
 constexpr int kRepackMinObjects = 48;                          // below this, shadow rays are never re-packed
 constexpr int kQueueRays = 64;                                 // compacted shadow-ray queue entries
-constexpr int kScratchBytes = kQueueRays * 8 * 4 + 96 * 4;     // queue + occlusion flags, per warp
+constexpr int kListEntries = 512;                              // shadow-candidate list of a work item (packet_collect)
+constexpr int kScratchBytes = kQueueRays * 8 * 4 + 96 * 4 + kListEntries * 4;   // queue + occlusion flags + list, per warp
 
 struct WarpCtx {
     uint32_t box_off4, sph_off4; // resident: float4 offsets of the staged hot lists in smem_f4
     uint32_t lrec_off4;          // resident: float4 offset of the staged per-light records
     float* queue;                // [kQueueRays][8]
     int* occ;                    // [96]
+    uint32_t* list;              // [kListEntries]: hot index | cone mask << 28
     uint32_t buf_off4[2];        // streaming double buffer (float4 offsets in smem_f4)
     uint32_t buf_addr[2];        // shared-space addresses of buf / barriers
     uint32_t bar_addr[2];
@@ -463,6 +465,7 @@ __device__ __forceinline__ void box_full_test(const RtParams& P, int idx, unsign
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const bool mine = (pm >> r) & 1u;
+        if (R > 1 && !__any_sync(kFull, mine)) continue;      // warp-uniform: no lane wants this ray slot tested
         if (COUNT) cnt.box_tests += mine;
         if (!SHARED) bo = box_origin(rec, o[r]);
         float tn, tf; Slabs s; V3 ld;
@@ -782,6 +785,271 @@ __device__ __forceinline__ void lights_tile(const RtParams& P, const float4* __r
     for (int r = 0; r < R; ++r) best_io[r] = best[r];
 }
 
+// -------------------------------------------------------------------------
+// Packet tests (large scenes, coherent rays).  The rays of a warp that leave one point -- the primary
+// rays of a work item (camera, glsl:391) or the shadow rays toward one light seen from the light
+// (glsl:808-809) -- lie inside a narrow cone.  The warp tests 32 objects per instruction against that
+// cone, one object per LANE (centre and padded bounding radius from the same 16-byte records), and
+// only the objects whose bounding sphere meets the cone go through the per-ray tests above, in
+// original order.  Still brute force -- every object of the scene is tested for every packet, no
+// hierarchy, no spatial sorting -- but one cone test stands for 96 (ray, object) bounding tests.
+//
+// Conservative by construction: a ray of the packet can only hit an object
+// whose bounding sphere, grown by `rp`'s padding, meets the cone: signed distance of the centre to the
+// cone's surface, p*cos(theta) - h*sin(theta) <= rp, with sin(theta) padded by 5e-4 relative + 4e-6
+// and p^2 = |v x axis|^2 (no cancellation).  The per-ray tests behind it are the ones of the loops
+// above, so a frame is byte-identical with the packet tests on or off (tests/test_gpu_parity.py).
+// -------------------------------------------------------------------------
+struct Cone {
+    V3 apex, axis;
+    float s, c2;      // padded sin(theta), 1 - s^2
+    float reach;      // no ray of the packet extends further than this from the apex
+};
+
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+    return mk(__fmaf_rn(a.y, b.z, -__fmul_rn(a.z, b.y)), __fmaf_rn(a.z, b.x, -__fmul_rn(a.x, b.z)),
+              __fmaf_rn(a.x, b.y, -__fmul_rn(a.y, b.x)));
+}
+__device__ __forceinline__ float warp_max_nonneg(float v) {      // v >= 0: floats order like their bit patterns
+    return __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(v)));
+}
+// c = (centre, .), rp = padded bounding radius (NaN for a box that can never be hit -> false)
+__device__ __forceinline__ bool cone_pass(const Cone& k, float4 c, float rp) {
+    const V3 v = mk(c.x - k.apex.x, c.y - k.apex.y, c.z - k.apex.z);
+    const float h = __fmaf_rn(v.x, k.axis.x, __fmaf_rn(v.y, k.axis.y, __fmul_rn(v.z, k.axis.z)));
+    const V3 x = cross3(v, k.axis);
+    const float p2 = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+    const float rhs = __fmaf_rn(h, k.s, rp);
+    const float far = k.reach + rp;
+    return rhs >= 0.0f && __fmul_rn(p2, k.c2) <= __fmul_rn(rhs, rhs) && __fmaf_rn(h, h, p2) <= __fmul_rn(far, far);
+}
+// Finishes a cone from the warp's maxima: s2 = max |axis x u|^2 over the packet's unit directions u.
+__device__ __forceinline__ void cone_close(Cone& k, float s2max, float reach) {
+    k.s = __fmaf_rn(sqrt_approx(s2max), 1.0005f, 4e-6f);
+    k.c2 = fmaxf(1.0f - k.s * k.s, 0.0f);
+    k.reach = reach;
+}
+constexpr float kConeMinCos = 0.6f;     // wider packets take the per-ray loops
+// Padded bounding radius of a record.  Boxes: w = padded squared circumradius (prologue).  Spheres: w = r*r,
+// padded here by the cancellation noise of the shader's quadratic (pad2 = 4e-6 E^2) and the coordinate
+// rounding (pad1 = 2e-6 E).  `grow`: what the packet's rays may be off their cone by (shadow rays: 0.0101).
+__device__ __forceinline__ float packet_radius(float w, bool sph, float grow, float pad1, float pad2) {
+    float rp = sqrt_approx(sph ? w + pad2 : w);
+    if (sph) rp = __fmaf_rn(rp, 1.0005f, pad1);
+    return __fmaf_rn(rp, 1.000001f, grow);
+}
+
+// The whole object loop for one packet of 3 rays per lane with a common origin `o` per lane: the
+// primary rays of a work item (closest hit: live_min = smallest positive float, glsl:753-776) or the
+// shadow rays of the warp's hit points (any hit below t = 1: live_min = 1, glsl:816).  One copy in the
+// instruction stream for both (out of line, runtime switches): with 16 warps per SM in different
+// phases of a frame the large-scene kernels are instruction-cache bound, not issue bound.
+template <bool SMEM, bool COUNT>
+__device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
+                                          float grow, float live_min, float pad1, float pad2, V3 o0,
+                                          const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
+                                          RtCounters& cnt) {
+    constexpr int R = kShadowBatch;
+    V3 o[R], d[R];
+    float best[R]; int bidx[R];
+    Cone cone[R];
+    float qe[R];
+    RayQ q[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        o[r] = o0; d[r] = d_in[r]; best[r] = best_io[r]; bidx[r] = bidx_io[r]; cone[r] = cone_in[r];
+        q[r] = ray_q(d[r]);
+        qe[r] = __fmul_rn(q[r].qa, 0.9999f);
+    }
+    const bool anyhit = live_min >= 1.0f;
+    const int lane = w.lane;
+    const int nbt = n_box_tiles<true>(P);
+    const int n_tiles = nbt + n_sph_tiles(P);
+    for (int t = 0; t < n_tiles; ++t) {
+        // no live ray left in the warp (shadow rays: every one occluded, glsl:816 needs ANY occluder)
+        if (!__any_sync(kFull, best[0] >= live_min || best[1] >= live_min || best[2] >= live_min)) {
+            if (t > 0) tile_drain<SMEM>(w, t - 1, n_tiles);
+            break;
+        }
+        if (t == 0) tile_begin<SMEM, true>(P, w);
+        const float4* __restrict__ recs = tile_acquire<SMEM, true>(P, w, t, n_tiles);
+        const bool sph = t >= nbt;
+        const int base = (sph ? t - nbt : t) * kTileSph;
+        const int n = min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
+        for (int i = 0; i < n; i += 32) {
+            const int j = i + lane;
+            const float4 c = recs[min(j, n - 1)];
+            const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
+            bool pass = false;
+#pragma unroll
+            for (int k = 0; k < R; ++k)
+                if ((on >> k) & 1u) pass = pass | cone_pass(cone[k], c, rp);      // no short circuit: lanes stay converged
+            if (COUNT && j < n) cnt.packet_tests += (unsigned long long)__popc(on);
+            unsigned mask = __ballot_sync(kFull, pass && j < n);
+            while (mask) {
+                const int idx = i + __ffs(mask) - 1;
+                mask &= mask - 1u;
+                const float4 cc = recs[idx];
+                const SphO so = sphere_origin(cc, o[0]);
+                if (!sph) {
+                    // per-ray bounding-sphere test, then the slab test (the slow path of boxes_tile_cull)
+                    unsigned m = 0u;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const bool live = best[r] >= live_min;
+                        if (COUNT) cnt.cull_tests += live;
+                        const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                        const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qe[r], so.qc));
+                        if (live && disc >= 0.0f) m |= 1u << r;
+                    }
+                    if (__any_sync(kFull, m != 0u))
+                        box_full_test<R, false, true, COUNT>(P, base + idx, m, o, d, best, bidx, cnt);
+                } else {
+                    // the discriminant of glsl:591, then the roots (the slow path of spheres_tile)
+                    float hb[R], disc[R];
+                    bool anyg = false;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const bool live = best[r] >= live_min;
+                        if (COUNT) cnt.cull_tests += live;
+                        hb[r] = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                        disc[r] = __fmaf_rn(hb[r], hb[r], -__fmul_rn(q[r].qa, so.qc));
+                        anyg = anyg || (live && disc[r] >= 0.0f);
+                    }
+                    if (__any_sync(kFull, anyg)) {
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            if (COUNT) cnt.sphere_tests += best[r] >= live_min && disc[r] >= 0.0f;
+                            const float sq = sqrt_approx(fmaxf(disc[r], 0.0f));
+                            const float tn = __fmul_rn(-hb[r] - sq, q[r].iqa);
+                            const float tf = __fmul_rn(sq - hb[r], q[r].iqa);
+                            const float tt = (disc[r] < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
+                            if (tt > 0.0f && tt < best[r]) { best[r] = tt; bidx[r] = P.n_box + base + idx; }
+                            else if (!anyhit && tt == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
+                                if (__ldg(P.sph_obj + base + idx) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + idx;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) { best_io[r] = best[r]; bidx_io[r] = bidx[r]; }
+}
+
+// The shadow rays of a whole work item (3 tiles x 32 hit points x up to 3 lights) against the scene in ONE
+// pass: cone k bounds the directions from light k to all hit points of the work item; the objects that
+// meet a cone are appended, in order, to the warp's candidate list (hot index | cone mask << 28).
+// Returns the number of entries, or -1 when the list overflowed (the caller then traces per tile).
+template <bool SMEM, bool COUNT>
+__device__ __noinline__ int packet_collect(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
+                                           float grow, float pad1, float pad2, RtCounters& cnt) {
+    constexpr int R = kShadowBatch;
+    Cone cone[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) cone[r] = cone_in[r];
+    const int lane = w.lane;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    uint32_t* __restrict__ list = w.list;
+    int count = 0;
+    const int nbt = n_box_tiles<true>(P);
+    const int n_tiles = nbt + n_sph_tiles(P);
+    tile_begin<SMEM, true>(P, w);
+    for (int t = 0; t < n_tiles; ++t) {
+        const float4* __restrict__ recs = tile_acquire<SMEM, true>(P, w, t, n_tiles);
+        const bool sph = t >= nbt;
+        const int base = (sph ? t - nbt : t) * kTileSph;
+        const int n = min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
+        const uint32_t hot0 = (uint32_t)(sph ? P.n_box + base : base);
+        for (int i = 0; i < n; i += 32) {
+            const int j = i + lane;
+            const float4 c = recs[min(j, n - 1)];
+            const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
+            unsigned cm = 0u;
+#pragma unroll
+            for (int k = 0; k < R; ++k)
+                if ((on >> k) & 1u) cm |= cone_pass(cone[k], c, rp) ? (1u << k) : 0u;
+            if (j >= n) cm = 0u;
+            if (COUNT && j < n) cnt.packet_tests += (unsigned long long)__popc(on);
+            const unsigned mask = __ballot_sync(kFull, cm != 0u);
+            if (mask) {
+                const int pos = count + __popc(mask & lt_mask);
+                if (cm != 0u && pos < kListEntries) list[pos] = (hot0 + (uint32_t)j) | (cm << 28);
+                count += __popc(mask);
+            }
+        }
+    }
+    __syncwarp();
+    return count <= kListEntries ? count : -1;
+}
+
+// The 3 shadow rays of one hit point per lane (ray r goes to light slot r) against the work item's
+// candidate list: per-ray bounding test, then the exact test, like the slow paths of the tile loops.
+template <bool SMEM, bool COUNT>
+__device__ __noinline__ void list_shadow(const RtParams& P, const WarpCtx& w, int count, V3 o0, const V3* __restrict__ d_in,
+                                         float* __restrict__ best_io, RtCounters& cnt) {
+    constexpr int R = kShadowBatch;
+    V3 o[R], d[R];
+    float best[R]; int bidx[R];
+    float qe[R];
+    RayQ q[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        o[r] = o0; d[r] = d_in[r]; best[r] = best_io[r]; bidx[r] = -1;
+        q[r] = ray_q(d[r]);
+        qe[r] = __fmul_rn(q[r].qa, 0.9999f);
+    }
+    const uint32_t* __restrict__ list = w.list;
+    const float4* __restrict__ res = smem_f4 + w.box_off4;      // resident: bounding records, boxes then spheres
+    auto record = [&](uint32_t ent) -> float4 {
+        const int idx = (int)(ent & 0x0fffffffu);
+        if (SMEM) return idx < P.n_box ? res[idx] : smem_f4[w.sph_off4 + (uint32_t)(idx - P.n_box)];
+        return idx < P.n_box ? __ldg(P.box_cull + idx) : __ldg(P.sph_hot + (idx - P.n_box));
+    };
+    uint32_t ent_n = count > 0 ? list[0] : 0u;
+    float4 cc_n = count > 0 ? record(ent_n) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    for (int e = 0; e < count; ++e) {
+        if (!__any_sync(kFull, best[0] >= 1.0f || best[1] >= 1.0f || best[2] >= 1.0f)) break;
+        const uint32_t ent = ent_n;
+        const float4 cc = cc_n;
+        if (e + 1 < count) { ent_n = list[e + 1]; cc_n = record(ent_n); }      // next record in flight (L2 when streaming)
+        const int idx = (int)(ent & 0x0fffffffu);
+        const unsigned cm = ent >> 28;
+        const SphO so = sphere_origin(cc, o[0]);
+        if (idx < P.n_box) {
+            unsigned m = 0u;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const bool live = best[r] >= 1.0f && ((cm >> r) & 1u);
+                if (COUNT) cnt.cull_tests += live;
+                const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qe[r], so.qc));
+                if (live && disc >= 0.0f) m |= 1u << r;
+            }
+            if (__any_sync(kFull, m != 0u))
+                box_full_test<R, false, true, COUNT>(P, idx, m, o, d, best, bidx, cnt);
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const bool live = best[r] >= 1.0f && ((cm >> r) & 1u);
+                if (COUNT) cnt.cull_tests += live;
+                const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(q[r].qa, so.qc));
+                if (!__any_sync(kFull, live && disc >= 0.0f)) continue;
+                if (COUNT) cnt.sphere_tests += live && disc >= 0.0f;
+                const float sq = sqrt_approx(fmaxf(disc, 0.0f));
+                const float tn = __fmul_rn(-hb - sq, q[r].iqa);
+                const float tf = __fmul_rn(sq - hb, q[r].iqa);
+                const float tt = (disc < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
+                if (live && tt > 0.0f && tt < best[r]) best[r] = tt;
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) best_io[r] = best[r];
+}
+
 // One tile, dispatched on its kind.
 template <int R, bool ANYHIT, bool SHARED, bool COUNT, bool CULL>
 __device__ __forceinline__ void any_tile(const RtParams& P, const float4* recs, int t,
@@ -972,6 +1240,42 @@ __device__ __forceinline__ void trace_shadow(const RtParams& P, WarpCtx& w, V3 s
 }
 
 // -------------------------------------------------------------------------
+// Shadow rays as packets: one cone per light slot, apex at the light, around the directions from
+// the light to the warp's hit points.  A shadow ray runs from p + 0.01 n along L - p (glsl:808-809),
+// so its line passes within 0.01 of L; the bounding radii grow by 0.0101 (`grow`) to cover that, and
+// nothing further from L than the farthest hit point (+ 0.0101) can occlude (t < 1, glsl:816).
+// Returns false (nothing traced) when some slot's directions spread beyond kConeMinCos.
+// -------------------------------------------------------------------------
+__device__ __forceinline__ bool shadow_cones(const WarpCtx& w, const V3 (&lp)[kShadowBatch], const V3 (&sd)[kShadowBatch],
+                                             const float (&sb)[kShadowBatch], Cone (&cone)[kShadowBatch], unsigned& on) {
+    on = 0u;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < kShadowBatch; ++k) {
+        const bool act = sb[k] >= 1.0f;
+        const unsigned am = __ballot_sync(kFull, act);
+        if (am == 0u) continue;
+        on |= 1u << k;
+        const float l2 = __fmaf_rn(sd[k].x, sd[k].x, __fmaf_rn(sd[k].y, sd[k].y, __fmul_rn(sd[k].z, sd[k].z)));
+        const float il = rsqrtf(l2);
+        const V3 u = mk(-sd[k].x * il, -sd[k].y * il, -sd[k].z * il);      // from the light toward the hit point
+        // axis: a lane near the middle of the 8x4 tile if it is active, else the first active lane
+        const unsigned mid = am & 0x00181800u;
+        const int lead = __ffs(mid ? mid : am) - 1;
+        cone[k].apex = lp[k];
+        cone[k].axis = mk(__shfl_sync(kFull, u.x, lead), __shfl_sync(kFull, u.y, lead), __shfl_sync(kFull, u.z, lead));
+        const V3 x = cross3(cone[k].axis, u);
+        const float s2 = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+        const float cs = dot3(cone[k].axis, u);
+        ok = ok && __all_sync(kFull, !act || cs >= kConeMinCos);             // NaN (zero-length ray) -> false
+        const float s2max = warp_max_nonneg(act ? fminf(s2, 1.0f) : 0.0f);
+        const float l2max = warp_max_nonneg(act ? l2 : 0.0f);
+        cone_close(cone[k], s2max, __fmaf_rn(sqrt_approx(l2max), 1.0001f, 0.0101f));
+    }
+    return ok;
+}
+
+// -------------------------------------------------------------------------
 // Closest-hit record: everything ads_phong_lighting and the bounce phases need
 // (glsl:561-573 Collision + the object's material).
 // -------------------------------------------------------------------------
@@ -1091,7 +1395,8 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // -------------------------------------------------------------------------
 template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
 __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool valid, V3 org, V3 dir,
-                                           bool have_first, float first_t, int first_idx, RtCounters& cnt) {
+                                           bool have_first, float first_t, int first_idx, int list_n,
+                                           float pk_pad1, float pk_pad2, RtCounters& cnt) {
     // pending rays: origin, direction, weight, remaining depth
     float stk[kStack][8];
     int sp = 0;
@@ -1121,9 +1426,11 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             best[0] = 0.0f;
         }
         // PHASE 0 (glsl:956-967)
+        bool use_list = false;      // root node with the work item's shadow-candidate list (packet_collect)
         if (have_first) {           // warp-uniform: the root ray was traced by the caller
             if (act) { best[0] = first_t; bidx[0] = first_idx; }
             have_first = false;
+            use_list = list_n >= 0;
         } else {
             trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, o[0], d[0], best[0], bidx[0], cnt);
         }
@@ -1218,7 +1525,28 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                         sb[r] = 0.0f;
                     }
                 }
-                if (REPACK && CULL && P.n_lit > 0) trace_shadow<SMEM, REPACK, COUNT, CULL, true>(P, w, so, sd, sb, n_slots, cnt);
+                bool traced = false;
+                if (REPACK && CULL && use_list) {
+                    list_shadow<SMEM, COUNT>(P, w, list_n, so, sd, sb, cnt);
+                    traced = true;
+                } else if (REPACK && CULL && P.packet) {
+                    // coherent hit points (the usual case for the shadow rays of primary hits): packet tests
+                    V3 lp[kShadowBatch];
+#pragma unroll
+                    for (int r = 0; r < kShadowBatch; ++r) {
+                        const RtLightDev* __restrict__ L = P.lights + li[r < n_slots ? r : 0];
+                        lp[r] = mk(L->position[0], L->position[1], L->position[2]);
+                    }
+                    Cone cone[kShadowBatch];
+                    unsigned on;
+                    if (shadow_cones(w, lp, sd, sb, cone, on)) {
+                        int unused[kShadowBatch] = {-1, -1, -1};
+                        packet_trace<SMEM, COUNT>(P, w, cone, on, 0.0101f, 1.0f, pk_pad1, pk_pad2, so, sd, sb, unused, cnt);
+                        traced = true;
+                    }
+                }
+                if (traced) {}
+                else if (REPACK && CULL && P.n_lit > 0) trace_shadow<SMEM, REPACK, COUNT, CULL, true>(P, w, so, sd, sb, n_slots, cnt);
                 else trace_shadow<SMEM, REPACK, COUNT, CULL, false>(P, w, so, sd, sb, n_slots, cnt);
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
@@ -1307,6 +1635,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
         float4* scratch = smem_f4 + off4 + (size_t)warp * (kScratchBytes / 16);
         w.queue = reinterpret_cast<float*>(scratch);
         w.occ = reinterpret_cast<int*>(scratch + kQueueRays * 2);
+        w.list = reinterpret_cast<uint32_t*>(scratch + kQueueRays * 2 + 96 / 4);
         off4 += (size_t)kWarps * (kScratchBytes / 16);
     }
     w.buf_off4[0] = w.buf_off4[1] = 0u;
@@ -1332,7 +1661,16 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     const long long n_tiles = (long long)tiles_per_frame * P.n_frames;
     const int lx = lane & 7, ly = lane >> 3;
 
+    // packet tests: radius pads that scale with the scene extent E (see rt_prologue_math.h)
+    float pk_pad1 = 0.0f, pk_pad2 = 0.0f;
+    if (CULL && P.packet) {
+        const float E = __ldg(P.extent);
+        pk_pad1 = 2e-6f * E;
+        pk_pad2 = 4e-6f * E * E;
+    }
+
     RtCounters cnt;
+    cnt.packet_tests = 0ull;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
     cnt.cull_tests = cnt.warp_iters = 0ull;
 
@@ -1370,7 +1708,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                 dir[q] = primary_dir(P, cam, px[q], py, jx, jy);
             }
             if (NP == 1) {
-                sum[0] = sum[0] + trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid[0], org, dir[0], false, 0.0f, -1, cnt);
+                sum[0] = sum[0] + trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid[0], org, dir[0], false, 0.0f, -1, -1, 0.0f, 0.0f, cnt);
             } else {
                 // PHASE 0 of the three root frames (glsl:956-967), shared origin
                 V3 o3[kShadowBatch];
@@ -1380,11 +1718,98 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                     o3[q] = org; bidx[q] = -1;
                     best[q] = valid[q] ? kFar : 0.0f;
                 }
-                const int n_obj_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
-                tile_begin<SMEM, CULL>(P, w);
-                for (int t = 0; t < n_obj_tiles; ++t) {
-                    const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_obj_tiles);
-                    any_tile<kShadowBatch, false, true, COUNT, CULL>(P, recs, t, o3, dir, best, bidx, cnt);
+                // The work item's primary rays as one packet: a cone from the camera around the direction
+                // through the middle of the 24x4-pixel strip.
+                Cone pc[kShadowBatch];
+                bool packet = false;
+                if (CULL && P.packet) {
+                    pc[0].apex = org;
+                    pc[0].axis = primary_dir(P, cam, tx * (8 * NP) + 4 * NP, P.y0 + ty * 4 + 2, 0.0f, 0.0f);
+                    float s2 = 0.0f;
+                    bool in_cone = true;
+#pragma unroll
+                    for (int q = 0; q < kShadowBatch; ++q) {
+                        const V3 x = cross3(pc[0].axis, dir[q]);
+                        const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+                        if (valid[q]) {
+                            s2 = fmaxf(s2, fminf(s2q, 1.0f));
+                            in_cone = in_cone && dot3(pc[0].axis, dir[q]) >= kConeMinCos;
+                        }
+                    }
+                    packet = __all_sync(kFull, in_cone);
+                    cone_close(pc[0], warp_max_nonneg(s2), kFar * 1.001f);
+                    pc[1] = pc[0]; pc[2] = pc[0];
+                }
+                if (CULL && packet) {
+                    packet_trace<SMEM, COUNT>(P, w, pc, 1u, 0.0f, 1e-45f, pk_pad1, pk_pad2, org, dir, best, bidx, cnt);
+                } else {
+                    const int n_obj_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
+                    tile_begin<SMEM, CULL>(P, w);
+                    for (int t = 0; t < n_obj_tiles; ++t) {
+                        const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_obj_tiles);
+                        any_tile<kShadowBatch, false, true, COUNT, CULL>(P, recs, t, o3, dir, best, bidx, cnt);
+                    }
+                }
+                // The shadow rays of all three tiles in one pass over the scene: per lit light, a cone from the
+                // light around the work item's hit points (o + t d here; the shaded point of resolve_hit differs
+                // by rounding only, covered by 10 * pad1 = 2e-5 E in `grow`), candidates into the warp's list.
+                int list_n = -1;
+                if (CULL && packet && !RT_STRICT && P.n_lit_batch > 0) {
+                    V3 pa[kShadowBatch]; bool hq[kShadowBatch];
+#pragma unroll
+                    for (int q = 0; q < kShadowBatch; ++q) {
+                        hq[q] = valid[q] && bidx[q] >= 0;
+                        pa[q] = mk(__fmaf_rn(best[q], dir[q].x, org.x), __fmaf_rn(best[q], dir[q].y, org.y), __fmaf_rn(best[q], dir[q].z, org.z));
+                    }
+                    if (!__any_sync(kFull, hq[0] || hq[1] || hq[2])) {
+                        list_n = 0;                                   // nothing was hit: no shadow rays
+                    } else {
+                        Cone lc[kShadowBatch];
+                        bool ok = true;
+                        unsigned on = 0u;
+#pragma unroll
+                        for (int k = 0; k < kShadowBatch; ++k) {
+                            if (k < P.n_lit_batch) {
+                                const RtLightDev* __restrict__ L = P.lights + P.lit[k];
+                                const V3 lp = mk(L->position[0], L->position[1], L->position[2]);
+                                V3 u[kShadowBatch]; float l2[kShadowBatch];
+                                V3 sum = mk(0.0f, 0.0f, 0.0f);
+#pragma unroll
+                                for (int q = 0; q < kShadowBatch; ++q) {
+                                    const V3 v = pa[q] - lp;
+                                    l2[q] = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
+                                    u[q] = v * rsqrtf(l2[q]);
+                                    if (hq[q]) sum = sum + u[q];
+                                }
+#pragma unroll
+                                for (int off = 16; off > 0; off >>= 1) {
+                                    sum.x += __shfl_xor_sync(kFull, sum.x, off);
+                                    sum.y += __shfl_xor_sync(kFull, sum.y, off);
+                                    sum.z += __shfl_xor_sync(kFull, sum.z, off);
+                                }
+                                lc[k].apex = lp;
+                                lc[k].axis = normalize3(sum);
+                                float s2 = 0.0f, lmax = 0.0f;
+                                bool in_cone = true;
+#pragma unroll
+                                for (int q = 0; q < kShadowBatch; ++q) {
+                                    const V3 x = cross3(lc[k].axis, u[q]);
+                                    const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+                                    if (hq[q]) {
+                                        s2 = fmaxf(s2, fminf(s2q, 1.0f));
+                                        lmax = fmaxf(lmax, l2[q]);
+                                        in_cone = in_cone && dot3(lc[k].axis, u[q]) >= kConeMinCos;   // NaN -> false
+                                    }
+                                }
+                                ok = ok && __all_sync(kFull, in_cone);
+                                cone_close(lc[k], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f + 10.0f * pk_pad1));
+                                on |= 1u << k;
+                            } else {
+                                lc[k] = pc[0];
+                            }
+                        }
+                        if (ok) list_n = packet_collect<SMEM, COUNT>(P, w, lc, on, 0.0101f + 10.0f * pk_pad1, pk_pad1, pk_pad2, cnt);
+                    }
                 }
                 // one copy of the bounce machinery in the instruction stream: rolled loop, selected operands
 #pragma unroll 1
@@ -1393,7 +1818,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                     const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
                     const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
                     const bool vq = q == 0 ? valid[0] : (q == 1 ? valid[1] : valid[2]);
-                    const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, cnt);
+                    const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, list_n, pk_pad1, pk_pad2, cnt);
                     if (q == 0) sum[0] = sum[0] + c;
                     else if (q == 1) sum[1] = sum[1] + c;
                     else sum[2] = sum[2] + c;
@@ -1429,10 +1854,10 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     if (COUNT) {
         // warp-reduce then one atomic per warp per counter
         if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
-        unsigned long long v[10] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
-                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters};
+        unsigned long long v[11] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests};
 #pragma unroll
-        for (int k = 0; k < 10; ++k) {
+        for (int k = 0; k < 11; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

@@ -195,10 +195,14 @@ def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
     on = tracer.render(sc, cam, w, h)                    # the shipped kernels (the counting twins are
     off = tracer.render(sc, cam, w, h, no_cull=1)        # separate instantiations)
     assert np.array_equal(on, off)
-    # bit 1: bounding-sphere test on, per-light shadow records off
-    assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=2))
+    # bit 2: no packet (cone) tests -> per-ray bounding tests with per-light shadow records; bit 1: without them
+    assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=4))
+    assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=6))
+    _, st_ray = tracer.render(sc, cam, w, h, want_stats=True, no_cull=4)
     assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
     assert st_off["cull_tests"] == 0 and st_on["cull_tests"] > 0
+    assert st_on["packet_tests"] > 0 and st_ray["packet_tests"] == 0 and st_off["packet_tests"] == 0
+    assert st_on["cull_tests"] < st_ray["cull_tests"]      # secondary rays (depth > 0) keep the per-ray loops
     assert st_on["box_tests"] < st_off["box_tests"] // 4
     canvas = np.empty_like(on)
     edges = [0, 37, 90, h]
@@ -219,6 +223,7 @@ def test_large_scene_kernel_with_spp_and_batch(tracer):
         assert np.array_equal(batch[k], tracer.render(sc, cams[k], w, h, spp=4))
     _check(batch[1], ob.render(sc, cams[1], w, h, spp=4), "scaled 200 spp4 batch frame 1", need_edges=False)
     assert np.array_equal(batch, tracer.render(sc, cams, w, h, spp=4, no_cull=1))
+    assert np.array_equal(batch, tracer.render(sc, cams, w, h, spp=4, no_cull=4))
     for (ww, hh) in [(1, 1), (23, 5), (25, 4), (49, 3)]:
         img = tracer.render(sc, cams[0], ww, hh)
         rep = compare(img, ob.render(sc, cams[0], ww, hh))
@@ -244,6 +249,7 @@ def test_device_prologue_matches_host_prologue_and_oracle():
             _check(a, ob.render(sc, cam, w, h), "device prologue %d objects" % sc.objects_count, need_edges=False)
             # bands and the bounding-test switch stay byte-identical under the device prologue too
             assert np.array_equal(a, dev.render(sc, cam, w, h, no_cull=1))
+            assert np.array_equal(a, dev.render(sc, cam, w, h, no_cull=4))
             top = dev.render(sc, cam, w, h, y0=0, y1=50, band_only=True)
             assert np.array_equal(top, a[:50])
             # a strict render after a device prologue falls back to the host records (op-for-op parity)
@@ -255,7 +261,7 @@ def test_device_prologue_matches_host_prologue_and_oracle():
 
 def _far_scene(cube_half):
     base = rt.builtin_scene(0.0, 1)
-    n = 64
+    n = 128
     objs = (rt.Object * n)()
     rng = np.random.default_rng(7)
     for i in range(n):
@@ -290,8 +296,8 @@ def test_bounding_sphere_test_far_and_tiny_objects(tracer):
     for half in (11.0, 3000.0):
         sc = _far_scene(half)
         on = tracer.render(sc, cam, 320, 180)
-        assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=1))
-        assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=2))
+        for mode in (1, 2, 4, 6):
+            assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=mode)), mode
         ref = ob.render(sc, cam, 320, 180)
         _check(tracer.render(sc, cam, 320, 180, strict=True), ref, "far/tiny objects strict", need_edges=False)
         if half < 100.0:
