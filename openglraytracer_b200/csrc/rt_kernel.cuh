@@ -252,15 +252,13 @@ constexpr int kTileBytes = kTileBox * RT_BOX_F4 * 16;
 constexpr int kTileSph = kTileBytes / 16;                      // spheres per tile
 constexpr int kRepackMinObjects = 48;                          // below this, shadow rays are never re-packed
 constexpr int kQueueRays = 64;                                 // compacted shadow-ray queue entries
-constexpr int kListEntries = 512;                              // shadow-candidate list of a work item (packet_collect)
-constexpr int kScratchBytes = kQueueRays * 8 * 4 + 96 * 4 + kListEntries * 4;   // queue + occlusion flags + list, per warp
+constexpr int kScratchBytes = kQueueRays * 8 * 4 + 96 * 4;     // queue + occlusion flags, per warp
 
 struct WarpCtx {
     uint32_t box_off4, sph_off4; // resident: float4 offsets of the staged hot lists in smem_f4
     uint32_t lrec_off4;          // resident: float4 offset of the staged per-light records
     float* queue;                // [kQueueRays][8]
     int* occ;                    // [96]
-    uint32_t* list;              // [kListEntries]: hot index | cone mask << 28
     uint32_t buf_off4[2];        // streaming double buffer (float4 offsets in smem_f4)
     uint32_t buf_addr[2];        // shared-space addresses of buf / barriers
     uint32_t bar_addr[2];
@@ -844,20 +842,22 @@ __device__ __forceinline__ float packet_radius(float w, bool sph, float grow, fl
 // shadow rays of the warp's hit points (any hit below t = 1: live_min = 1, glsl:816).  One copy in the
 // instruction stream for both (out of line, runtime switches): with 16 warps per SM in different
 // phases of a frame the large-scene kernels are instruction-cache bound, not issue bound.
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool COUNT, int NC>
 __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
-                                          float grow, float live_min, float pad1, float pad2, V3 o0,
+                                          float grow, float live_min, float pad1, float pad2, bool shared, const V3* __restrict__ o_in,
                                           const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
                                           RtCounters& cnt) {
     constexpr int R = kShadowBatch;
     V3 o[R], d[R];
     float best[R]; int bidx[R];
-    Cone cone[R];
+    Cone cone[NC];
     float qe[R];
     RayQ q[R];
 #pragma unroll
+    for (int k = 0; k < NC; ++k) cone[k] = cone_in[k];
+#pragma unroll
     for (int r = 0; r < R; ++r) {
-        o[r] = o0; d[r] = d_in[r]; best[r] = best_io[r]; bidx[r] = bidx_io[r]; cone[r] = cone_in[r];
+        o[r] = o_in[r]; d[r] = d_in[r]; best[r] = best_io[r]; bidx[r] = bidx_io[r];
         q[r] = ray_q(d[r]);
         qe[r] = __fmul_rn(q[r].qa, 0.9999f);
     }
@@ -876,178 +876,102 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
         const bool sph = t >= nbt;
         const int base = (sph ? t - nbt : t) * kTileSph;
         const int n = min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
-        for (int i = 0; i < n; i += 32) {
-            const int j = i + lane;
-            const float4 c = recs[min(j, n - 1)];
-            const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
-            bool pass = false;
+        const uint32_t ra = smem_addr(recs);
+        // one cone: two objects per lane and iteration (64 objects per trip, two independent dependency
+        // chains); three cones: one object per lane (the six chains of two would spill)
+        constexpr int kHalves = NC == 1 ? 2 : 1;
+        for (int i0 = 0; i0 < n; i0 += 32 * kHalves) {
+            const int j0 = i0 + lane, j1 = j0 + 32;
+            const float4 c0 = lds128(ra + (uint32_t)min(j0, n - 1) * 16u);
+            const float rp0 = packet_radius(c0.w, sph, grow, pad1, pad2);
+            float4 c1 = c0;
+            float rp1 = rp0;
+            if (kHalves == 2) {
+                c1 = lds128(ra + (uint32_t)min(j1, n - 1) * 16u);
+                rp1 = packet_radius(c1.w, sph, grow, pad1, pad2);
+            }
+            bool pass0 = false, pass1 = false;
 #pragma unroll
-            for (int k = 0; k < R; ++k)
-                if ((on >> k) & 1u) pass = pass | cone_pass(cone[k], c, rp);      // no short circuit: lanes stay converged
-            if (COUNT && j < n) cnt.packet_tests += (unsigned long long)__popc(on);
-            unsigned mask = __ballot_sync(kFull, pass && j < n);
+            for (int k = 0; k < NC; ++k) {
+                if (NC == 1 || ((on >> k) & 1u)) {                  // no short circuit: lanes stay converged
+                    pass0 = pass0 | cone_pass(cone[k], c0, rp0);
+                    if (kHalves == 2) pass1 = pass1 | cone_pass(cone[k], c1, rp1);
+                }
+            }
+            if (COUNT) cnt.packet_tests += (unsigned long long)((NC == 1 ? 1 : __popc(on)) * ((j0 < n) + (kHalves == 2 && j1 < n)));
+            const unsigned mask0 = __ballot_sync(kFull, pass0 && j0 < n);
+            const unsigned mask1 = kHalves == 2 ? __ballot_sync(kFull, pass1 && j1 < n) : 0u;
+            if ((mask0 | mask1) == 0u) continue;
+#pragma unroll 1
+            for (int half = 0; half < kHalves; ++half) {
+            unsigned mask = half ? mask1 : mask0;
+            const int i = i0 + 32 * half;
             while (mask) {
                 const int idx = i + __ffs(mask) - 1;
                 mask &= mask - 1u;
-                const float4 cc = recs[idx];
-                const SphO so = sphere_origin(cc, o[0]);
+                const float4 cc = lds128(ra + (uint32_t)idx * 16u);
                 if (!sph) {
-                    // per-ray bounding-sphere test, then the slab test (the slow path of boxes_tile_cull)
+                    // per-ray bounding-sphere test, then the slab test (the slow path of boxes_tile_cull);
+                    // `shared` (warp-uniform): the three rays of a lane start at one point, one origin transform
                     unsigned m = 0u;
+                    SphO so;
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
+                        if (r == 0 || !shared) so = sphere_origin(cc, o[r]);
                         const bool live = best[r] >= live_min;
                         if (COUNT) cnt.cull_tests += live;
                         const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
                         const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qe[r], so.qc));
                         if (live && disc >= 0.0f) m |= 1u << r;
                     }
-                    if (__any_sync(kFull, m != 0u))
-                        box_full_test<R, false, true, COUNT>(P, base + idx, m, o, d, best, bidx, cnt);
-                } else {
-                    // the discriminant of glsl:591, then the roots (the slow path of spheres_tile)
-                    float hb[R], disc[R];
-                    bool anyg = false;
+                    if (__any_sync(kFull, m != 0u)) {
+                        const float4* __restrict__ g = P.box_hot + (size_t)(base + idx) * RT_BOX_F4;
+                        float4 rec[RT_BOX_F4];
 #pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        const bool live = best[r] >= live_min;
-                        if (COUNT) cnt.cull_tests += live;
-                        hb[r] = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
-                        disc[r] = __fmaf_rn(hb[r], hb[r], -__fmul_rn(q[r].qa, so.qc));
-                        anyg = anyg || (live && disc[r] >= 0.0f);
-                    }
-                    if (__any_sync(kFull, anyg)) {
+                        for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = __ldg(g + k);
+                        V3 bo;
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
-                            if (COUNT) cnt.sphere_tests += best[r] >= live_min && disc[r] >= 0.0f;
-                            const float sq = sqrt_approx(fmaxf(disc[r], 0.0f));
-                            const float tn = __fmul_rn(-hb[r] - sq, q[r].iqa);
-                            const float tf = __fmul_rn(sq - hb[r], q[r].iqa);
-                            const float tt = (disc[r] < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
-                            if (tt > 0.0f && tt < best[r]) { best[r] = tt; bidx[r] = P.n_box + base + idx; }
-                            else if (!anyhit && tt == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
-                                if (__ldg(P.sph_obj + base + idx) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + idx;
-                            }
+                            const bool mine = (m >> r) & 1u;
+                            if (r == 0 || !shared) bo = box_origin(rec, o[r]);
+                            if (!__any_sync(kFull, mine)) continue;       // warp-uniform: no lane wants this ray slot tested
+                            if (COUNT) cnt.box_tests += mine;
+                            float tn, tf; Slabs sl; V3 ld;
+                            box_slabs(rec, bo, d[r], tn, tf, sl, ld);
+                            const float tt = box_pick(tn, tf);
+                            // `mine` keeps the outcome a function of the ray alone (not of which lanes share its warp)
+                            if (mine && !box_reject(tn, tf) && tt > 0.0f && tt < best[r]) { best[r] = tt; bidx[r] = base + idx; }
+                        }
+                    }
+                } else {
+                    // the discriminant of glsl:591, then the roots (the slow path of spheres_tile), ray slot by ray slot
+#pragma unroll
+                    SphO so;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        if (r == 0 || !shared) so = sphere_origin(cc, o[r]);
+                        const bool live = best[r] >= live_min;
+                        if (COUNT) cnt.cull_tests += live;
+                        const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
+                        const float disc = __fmaf_rn(hb, hb, -__fmul_rn(q[r].qa, so.qc));
+                        if (!__any_sync(kFull, live && disc >= 0.0f)) continue;
+                        if (COUNT) cnt.sphere_tests += live && disc >= 0.0f;
+                        const float sq = sqrt_approx(fmaxf(disc, 0.0f));
+                        const float tn = __fmul_rn(-hb - sq, q[r].iqa);
+                        const float tf = __fmul_rn(sq - hb, q[r].iqa);
+                        const float tt = (disc < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
+                        if (tt > 0.0f && tt < best[r]) { best[r] = tt; bidx[r] = P.n_box + base + idx; }
+                        else if (!anyhit && tt == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
+                            if (__ldg(P.sph_obj + base + idx) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + idx;
                         }
                     }
                 }
+            }
             }
         }
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) { best_io[r] = best[r]; bidx_io[r] = bidx[r]; }
-}
-
-// The shadow rays of a whole work item (3 tiles x 32 hit points x up to 3 lights) against the scene in ONE
-// pass: cone k bounds the directions from light k to all hit points of the work item; the objects that
-// meet a cone are appended, in order, to the warp's candidate list (hot index | cone mask << 28).
-// Returns the number of entries, or -1 when the list overflowed (the caller then traces per tile).
-template <bool SMEM, bool COUNT>
-__device__ __noinline__ int packet_collect(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
-                                           float grow, float pad1, float pad2, RtCounters& cnt) {
-    constexpr int R = kShadowBatch;
-    Cone cone[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) cone[r] = cone_in[r];
-    const int lane = w.lane;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    uint32_t* __restrict__ list = w.list;
-    int count = 0;
-    const int nbt = n_box_tiles<true>(P);
-    const int n_tiles = nbt + n_sph_tiles(P);
-    tile_begin<SMEM, true>(P, w);
-    for (int t = 0; t < n_tiles; ++t) {
-        const float4* __restrict__ recs = tile_acquire<SMEM, true>(P, w, t, n_tiles);
-        const bool sph = t >= nbt;
-        const int base = (sph ? t - nbt : t) * kTileSph;
-        const int n = min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
-        const uint32_t hot0 = (uint32_t)(sph ? P.n_box + base : base);
-        for (int i = 0; i < n; i += 32) {
-            const int j = i + lane;
-            const float4 c = recs[min(j, n - 1)];
-            const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
-            unsigned cm = 0u;
-#pragma unroll
-            for (int k = 0; k < R; ++k)
-                if ((on >> k) & 1u) cm |= cone_pass(cone[k], c, rp) ? (1u << k) : 0u;
-            if (j >= n) cm = 0u;
-            if (COUNT && j < n) cnt.packet_tests += (unsigned long long)__popc(on);
-            const unsigned mask = __ballot_sync(kFull, cm != 0u);
-            if (mask) {
-                const int pos = count + __popc(mask & lt_mask);
-                if (cm != 0u && pos < kListEntries) list[pos] = (hot0 + (uint32_t)j) | (cm << 28);
-                count += __popc(mask);
-            }
-        }
-    }
-    __syncwarp();
-    return count <= kListEntries ? count : -1;
-}
-
-// The 3 shadow rays of one hit point per lane (ray r goes to light slot r) against the work item's
-// candidate list: per-ray bounding test, then the exact test, like the slow paths of the tile loops.
-template <bool SMEM, bool COUNT>
-__device__ __noinline__ void list_shadow(const RtParams& P, const WarpCtx& w, int count, V3 o0, const V3* __restrict__ d_in,
-                                         float* __restrict__ best_io, RtCounters& cnt) {
-    constexpr int R = kShadowBatch;
-    V3 o[R], d[R];
-    float best[R]; int bidx[R];
-    float qe[R];
-    RayQ q[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        o[r] = o0; d[r] = d_in[r]; best[r] = best_io[r]; bidx[r] = -1;
-        q[r] = ray_q(d[r]);
-        qe[r] = __fmul_rn(q[r].qa, 0.9999f);
-    }
-    const uint32_t* __restrict__ list = w.list;
-    const float4* __restrict__ res = smem_f4 + w.box_off4;      // resident: bounding records, boxes then spheres
-    auto record = [&](uint32_t ent) -> float4 {
-        const int idx = (int)(ent & 0x0fffffffu);
-        if (SMEM) return idx < P.n_box ? res[idx] : smem_f4[w.sph_off4 + (uint32_t)(idx - P.n_box)];
-        return idx < P.n_box ? __ldg(P.box_cull + idx) : __ldg(P.sph_hot + (idx - P.n_box));
-    };
-    uint32_t ent_n = count > 0 ? list[0] : 0u;
-    float4 cc_n = count > 0 ? record(ent_n) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    for (int e = 0; e < count; ++e) {
-        if (!__any_sync(kFull, best[0] >= 1.0f || best[1] >= 1.0f || best[2] >= 1.0f)) break;
-        const uint32_t ent = ent_n;
-        const float4 cc = cc_n;
-        if (e + 1 < count) { ent_n = list[e + 1]; cc_n = record(ent_n); }      // next record in flight (L2 when streaming)
-        const int idx = (int)(ent & 0x0fffffffu);
-        const unsigned cm = ent >> 28;
-        const SphO so = sphere_origin(cc, o[0]);
-        if (idx < P.n_box) {
-            unsigned m = 0u;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const bool live = best[r] >= 1.0f && ((cm >> r) & 1u);
-                if (COUNT) cnt.cull_tests += live;
-                const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
-                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qe[r], so.qc));
-                if (live && disc >= 0.0f) m |= 1u << r;
-            }
-            if (__any_sync(kFull, m != 0u))
-                box_full_test<R, false, true, COUNT>(P, idx, m, o, d, best, bidx, cnt);
-        } else {
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const bool live = best[r] >= 1.0f && ((cm >> r) & 1u);
-                if (COUNT) cnt.cull_tests += live;
-                const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
-                const float disc = __fmaf_rn(hb, hb, -__fmul_rn(q[r].qa, so.qc));
-                if (!__any_sync(kFull, live && disc >= 0.0f)) continue;
-                if (COUNT) cnt.sphere_tests += live && disc >= 0.0f;
-                const float sq = sqrt_approx(fmaxf(disc, 0.0f));
-                const float tn = __fmul_rn(-hb - sq, q[r].iqa);
-                const float tf = __fmul_rn(sq - hb, q[r].iqa);
-                const float tt = (disc < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
-                if (live && tt > 0.0f && tt < best[r]) best[r] = tt;
-            }
-        }
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) best_io[r] = best[r];
 }
 
 // One tile, dispatched on its kind.
@@ -1395,7 +1319,7 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // -------------------------------------------------------------------------
 template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
 __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool valid, V3 org, V3 dir,
-                                           bool have_first, float first_t, int first_idx, int list_n,
+                                           bool have_first, float first_t, int first_idx, bool have_sb, const float (&first_sb)[kShadowBatch],
                                            float pk_pad1, float pk_pad2, RtCounters& cnt) {
     // pending rays: origin, direction, weight, remaining depth
     float stk[kStack][8];
@@ -1426,11 +1350,11 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             best[0] = 0.0f;
         }
         // PHASE 0 (glsl:956-967)
-        bool use_list = false;      // root node with the work item's shadow-candidate list (packet_collect)
+        bool root_sb = false;       // root node whose shadow rays the caller has traced (root_shadows)
         if (have_first) {           // warp-uniform: the root ray was traced by the caller
             if (act) { best[0] = first_t; bidx[0] = first_idx; }
             have_first = false;
-            use_list = list_n >= 0;
+            root_sb = have_sb;
         } else {
             trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, o[0], d[0], best[0], bidx[0], cnt);
         }
@@ -1526,8 +1450,9 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                     }
                 }
                 bool traced = false;
-                if (REPACK && CULL && use_list) {
-                    list_shadow<SMEM, COUNT>(P, w, list_n, so, sd, sb, cnt);
+                if (REPACK && CULL && root_sb) {
+#pragma unroll
+                    for (int r = 0; r < kShadowBatch; ++r) sb[r] = sb[r] >= 1.0f ? first_sb[r] : sb[r];
                     traced = true;
                 } else if (REPACK && CULL && P.packet) {
                     // coherent hit points (the usual case for the shadow rays of primary hits): packet tests
@@ -1541,7 +1466,8 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                     unsigned on;
                     if (shadow_cones(w, lp, sd, sb, cone, on)) {
                         int unused[kShadowBatch] = {-1, -1, -1};
-                        packet_trace<SMEM, COUNT>(P, w, cone, on, 0.0101f, 1.0f, pk_pad1, pk_pad2, so, sd, sb, unused, cnt);
+                        V3 so3[kShadowBatch] = {so, so, so};
+                        packet_trace<SMEM, COUNT, kShadowBatch>(P, w, cone, on, 0.0101f, 1.0f, pk_pad1, pk_pad2, true, so3, sd, sb, unused, cnt);
                         traced = true;
                     }
                 }
@@ -1635,7 +1561,6 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
         float4* scratch = smem_f4 + off4 + (size_t)warp * (kScratchBytes / 16);
         w.queue = reinterpret_cast<float*>(scratch);
         w.occ = reinterpret_cast<int*>(scratch + kQueueRays * 2);
-        w.list = reinterpret_cast<uint32_t*>(scratch + kQueueRays * 2 + 96 / 4);
         off4 += (size_t)kWarps * (kScratchBytes / 16);
     }
     w.buf_off4[0] = w.buf_off4[1] = 0u;
@@ -1707,8 +1632,9 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                 jitter(P, px[q], py, s, jx, jy);
                 dir[q] = primary_dir(P, cam, px[q], py, jx, jy);
             }
+            const float no_sb[kShadowBatch] = {0.0f, 0.0f, 0.0f};
             if (NP == 1) {
-                sum[0] = sum[0] + trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid[0], org, dir[0], false, 0.0f, -1, -1, 0.0f, 0.0f, cnt);
+                sum[0] = sum[0] + trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid[0], org, dir[0], false, 0.0f, -1, false, no_sb, 0.0f, 0.0f, cnt);
             } else {
                 // PHASE 0 of the three root frames (glsl:956-967), shared origin
                 V3 o3[kShadowBatch];
@@ -1720,7 +1646,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                 }
                 // The work item's primary rays as one packet: a cone from the camera around the direction
                 // through the middle of the 24x4-pixel strip.
-                Cone pc[kShadowBatch];
+                Cone pc[1];
                 bool packet = false;
                 if (CULL && P.packet) {
                     pc[0].apex = org;
@@ -1738,10 +1664,9 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                     }
                     packet = __all_sync(kFull, in_cone);
                     cone_close(pc[0], warp_max_nonneg(s2), kFar * 1.001f);
-                    pc[1] = pc[0]; pc[2] = pc[0];
                 }
                 if (CULL && packet) {
-                    packet_trace<SMEM, COUNT>(P, w, pc, 1u, 0.0f, 1e-45f, pk_pad1, pk_pad2, org, dir, best, bidx, cnt);
+                    packet_trace<SMEM, COUNT, 1>(P, w, pc, 1u, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
                 } else {
                     const int n_obj_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
                     tile_begin<SMEM, CULL>(P, w);
@@ -1750,65 +1675,89 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                         any_tile<kShadowBatch, false, true, COUNT, CULL>(P, recs, t, o3, dir, best, bidx, cnt);
                     }
                 }
-                // The shadow rays of all three tiles in one pass over the scene: per lit light, a cone from the
-                // light around the work item's hit points (o + t d here; the shaded point of resolve_hit differs
-                // by rounding only, covered by 10 * pad1 = 2e-5 E in `grow`), candidates into the warp's list.
-                int list_n = -1;
+                // The shadow rays of the three root hits, light by light: pass k traces, for every lane, the rays
+                // from its three hit points toward lit light k (glsl:807-819) as ONE packet -- a cone from the
+                // light around the work item's 96 hit points -- instead of three packets of three cones each.
+                // so / sd are built exactly as the shading code builds them (resolve_hit is deterministic).
+                bool have_sb = false;
+                float rsb[kShadowBatch][kShadowBatch];       // [tile q][light slot]
+#pragma unroll
+                for (int q = 0; q < kShadowBatch; ++q)
+#pragma unroll
+                    for (int k = 0; k < kShadowBatch; ++k) rsb[q][k] = 0.0f;
                 if (CULL && packet && !RT_STRICT && P.n_lit_batch > 0) {
-                    V3 pa[kShadowBatch]; bool hq[kShadowBatch];
-#pragma unroll
+                    V3 hp[kShadowBatch], so3[kShadowBatch];
+                    bool sh[kShadowBatch];
+#pragma unroll 1
                     for (int q = 0; q < kShadowBatch; ++q) {
-                        hq[q] = valid[q] && bidx[q] >= 0;
-                        pa[q] = mk(__fmaf_rn(best[q], dir[q].x, org.x), __fmaf_rn(best[q], dir[q].y, org.y), __fmaf_rn(best[q], dir[q].z, org.z));
+                        const V3 dq = q == 0 ? dir[0] : (q == 1 ? dir[1] : dir[2]);
+                        const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
+                        const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
+                        const bool vq = q == 0 ? valid[0] : (q == 1 ? valid[1] : valid[2]);
+                        bool shade = false;
+                        V3 p = mk(0.0f, 0.0f, 0.0f), so = mk(0.0f, 0.0f, 0.0f);
+                        if (vq && iq >= 0) {
+                            const Hit h = resolve_hit<SMEM, CULL>(P, w, org, dq, tq, iq);
+                            const RtCold* __restrict__ mat = P.cold + h.obj;
+                            // the weight of the Phong term, as trace_sample computes it for the root node
+                            float wp = 1.0f;
+                            if (P.max_depth > 0 && mat->reflectivity > 0.0f) wp = wp * (1.0f - mat->reflectivity);
+                            if (P.max_depth > 0 && mat->transparency > 0.0f) wp = wp * (1.0f - mat->transparency);
+                            shade = wp != 0.0f;
+                            p = h.p;
+                            so = h.p + h.n * 0.01f;                                            // glsl:808
+                        }
+                        if (q == 0) { hp[0] = p; so3[0] = so; sh[0] = shade; }
+                        else if (q == 1) { hp[1] = p; so3[1] = so; sh[1] = shade; }
+                        else { hp[2] = p; so3[2] = so; sh[2] = shade; }
                     }
-                    if (!__any_sync(kFull, hq[0] || hq[1] || hq[2])) {
-                        list_n = 0;                                   // nothing was hit: no shadow rays
-                    } else {
-                        Cone lc[kShadowBatch];
-                        bool ok = true;
-                        unsigned on = 0u;
+                    have_sb = true;
+                    if (__any_sync(kFull, sh[0] || sh[1] || sh[2])) {
+#pragma unroll 1
+                        for (int k = 0; k < P.n_lit_batch; ++k) {
+                            const RtLightDev* __restrict__ L = P.lights + P.lit[k];
+                            const V3 lp = mk(L->position[0], L->position[1], L->position[2]);
+                            V3 sd3[kShadowBatch], u[kShadowBatch];
+                            float l2[kShadowBatch], sbk[kShadowBatch];
+                            V3 sum = mk(0.0f, 0.0f, 0.0f);
 #pragma unroll
-                        for (int k = 0; k < kShadowBatch; ++k) {
-                            if (k < P.n_lit_batch) {
-                                const RtLightDev* __restrict__ L = P.lights + P.lit[k];
-                                const V3 lp = mk(L->position[0], L->position[1], L->position[2]);
-                                V3 u[kShadowBatch]; float l2[kShadowBatch];
-                                V3 sum = mk(0.0f, 0.0f, 0.0f);
+                            for (int q = 0; q < kShadowBatch; ++q) {
+                                sd3[q] = sh[q] ? mk(lp.x - hp[q].x, lp.y - hp[q].y, lp.z - hp[q].z) : mk(0.0f, 0.0f, 1.0f);   // glsl:809
+                                sbk[q] = sh[q] ? 1.0f : 0.0f;
+                                l2[q] = __fmaf_rn(sd3[q].x, sd3[q].x, __fmaf_rn(sd3[q].y, sd3[q].y, __fmul_rn(sd3[q].z, sd3[q].z)));
+                                u[q] = sd3[q] * -rsqrtf(l2[q]);                                // from the light toward the hit point
+                                if (sh[q]) sum = sum + u[q];
+                            }
 #pragma unroll
-                                for (int q = 0; q < kShadowBatch; ++q) {
-                                    const V3 v = pa[q] - lp;
-                                    l2[q] = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
-                                    u[q] = v * rsqrtf(l2[q]);
-                                    if (hq[q]) sum = sum + u[q];
+                            for (int off = 16; off > 0; off >>= 1) {
+                                sum.x += __shfl_xor_sync(kFull, sum.x, off);
+                                sum.y += __shfl_xor_sync(kFull, sum.y, off);
+                                sum.z += __shfl_xor_sync(kFull, sum.z, off);
+                            }
+                            Cone lc[1];
+                            lc[0].apex = lp;
+                            lc[0].axis = normalize3(sum);
+                            float s2 = 0.0f, lmax = 0.0f;
+                            bool in_cone = true;
+#pragma unroll
+                            for (int q = 0; q < kShadowBatch; ++q) {
+                                const V3 x = cross3(lc[0].axis, u[q]);
+                                const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+                                if (sh[q]) {
+                                    s2 = fmaxf(s2, fminf(s2q, 1.0f));
+                                    lmax = fmaxf(lmax, l2[q]);
+                                    in_cone = in_cone && dot3(lc[0].axis, u[q]) >= kConeMinCos;     // NaN -> false
                                 }
+                            }
+                            if (!__all_sync(kFull, in_cone)) { have_sb = false; break; }          // wide packet: per tile below
+                            cone_close(lc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
+                            int unused[kShadowBatch] = {-1, -1, -1};
+                            packet_trace<SMEM, COUNT, 1>(P, w, lc, 1u, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
 #pragma unroll
-                                for (int off = 16; off > 0; off >>= 1) {
-                                    sum.x += __shfl_xor_sync(kFull, sum.x, off);
-                                    sum.y += __shfl_xor_sync(kFull, sum.y, off);
-                                    sum.z += __shfl_xor_sync(kFull, sum.z, off);
-                                }
-                                lc[k].apex = lp;
-                                lc[k].axis = normalize3(sum);
-                                float s2 = 0.0f, lmax = 0.0f;
-                                bool in_cone = true;
-#pragma unroll
-                                for (int q = 0; q < kShadowBatch; ++q) {
-                                    const V3 x = cross3(lc[k].axis, u[q]);
-                                    const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
-                                    if (hq[q]) {
-                                        s2 = fmaxf(s2, fminf(s2q, 1.0f));
-                                        lmax = fmaxf(lmax, l2[q]);
-                                        in_cone = in_cone && dot3(lc[k].axis, u[q]) >= kConeMinCos;   // NaN -> false
-                                    }
-                                }
-                                ok = ok && __all_sync(kFull, in_cone);
-                                cone_close(lc[k], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f + 10.0f * pk_pad1));
-                                on |= 1u << k;
-                            } else {
-                                lc[k] = pc[0];
+                            for (int q = 0; q < kShadowBatch; ++q) {
+                                if (k == 0) rsb[q][0] = sbk[q]; else if (k == 1) rsb[q][1] = sbk[q]; else rsb[q][2] = sbk[q];
                             }
                         }
-                        if (ok) list_n = packet_collect<SMEM, COUNT>(P, w, lc, on, 0.0101f + 10.0f * pk_pad1, pk_pad1, pk_pad2, cnt);
                     }
                 }
                 // one copy of the bounce machinery in the instruction stream: rolled loop, selected operands
@@ -1818,7 +1767,10 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                     const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
                     const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
                     const bool vq = q == 0 ? valid[0] : (q == 1 ? valid[1] : valid[2]);
-                    const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, list_n, pk_pad1, pk_pad2, cnt);
+                    float fsb[kShadowBatch];
+#pragma unroll
+                    for (int k = 0; k < kShadowBatch; ++k) fsb[k] = q == 0 ? rsb[0][k] : (q == 1 ? rsb[1][k] : rsb[2][k]);
+                    const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, have_sb, fsb, pk_pad1, pk_pad2, cnt);
                     if (q == 0) sum[0] = sum[0] + c;
                     else if (q == 1) sum[1] = sum[1] + c;
                     else sum[2] = sum[2] + c;
