@@ -863,24 +863,35 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
     }
     const bool anyhit = live_min >= 1.0f;
     const int lane = w.lane;
-    const int nbt = n_box_tiles<true>(P);
-    const int n_tiles = nbt + n_sph_tiles(P);
+    // resident: each list is one "tile" in shared memory; streaming: kTileSph-record tiles through the warp's double buffer
+    const int nbt = SMEM ? 1 : n_box_tiles<true>(P);
+    const int n_tiles = nbt + (SMEM ? 1 : n_sph_tiles(P));
     for (int t = 0; t < n_tiles; ++t) {
         // no live ray left in the warp (shadow rays: every one occluded, glsl:816 needs ANY occluder)
         if (!__any_sync(kFull, best[0] >= live_min || best[1] >= live_min || best[2] >= live_min)) {
             if (t > 0) tile_drain<SMEM>(w, t - 1, n_tiles);
             break;
         }
-        if (t == 0) tile_begin<SMEM, true>(P, w);
-        const float4* __restrict__ recs = tile_acquire<SMEM, true>(P, w, t, n_tiles);
         const bool sph = t >= nbt;
-        const int base = (sph ? t - nbt : t) * kTileSph;
-        const int n = min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
-        const uint32_t ra = smem_addr(recs);
+        const int base = SMEM ? 0 : (sph ? t - nbt : t) * kTileSph;
+        const int n = SMEM ? (sph ? P.n_sph : P.n_box) : min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
+        uint32_t ra;
+        if (SMEM) {
+            ra = smem_addr(smem_f4 + (sph ? w.sph_off4 : w.box_off4));
+        } else {
+            if (t == 0 && lane == 0) tile_issue<true>(P, w, 0);
+            __syncwarp();                                     // every lane is done reading buffer (t+1)&1 (tile t-1)
+            if (lane == 0 && t + 1 < n_tiles) tile_issue<true>(P, w, t + 1);
+            tile_wait(w, t & 1);
+            ra = w.buf_addr[t & 1];
+        }
         // one cone: two objects per lane and iteration (64 objects per trip, two independent dependency
         // chains); three cones: one object per lane (the six chains of two would spill)
         constexpr int kHalves = NC == 1 ? 2 : 1;
         for (int i0 = 0; i0 < n; i0 += 32 * kHalves) {
+            // shadow packets: leave as soon as every ray of the warp is occluded (checked every 256 objects)
+            if (anyhit && (i0 & 255) == 0 && i0 > 0 &&
+                !__any_sync(kFull, best[0] >= 1.0f || best[1] >= 1.0f || best[2] >= 1.0f)) break;
             const int j0 = i0 + lane, j1 = j0 + 32;
             const float4 c0 = lds128(ra + (uint32_t)min(j0, n - 1) * 16u);
             const float rp0 = packet_radius(c0.w, sph, grow, pad1, pad2);
