@@ -135,7 +135,9 @@ typedef struct rt_options {
                                * _ALWAYS (1), _NEVER (2: device frame + device->host copy) */
     int32_t no_cull;          /* A/B switches, same image: bit 0 = large scenes run every slab test (no bounding-sphere
                                * test first); bit 1 = shadow rays do not use the per-light records; bit 2 = no packet
-                               * (cone) tests, every ray meets every bounding sphere itself */
+                               * (cone) tests, every ray meets every bounding sphere itself; bit 3 = no CTA-level packet
+                               * tests (each warp scans the scene for its own packets); bit 4 = CTA-level packet tests
+                               * also below RT_BLOCK_MIN_OBJECTS objects (test switch) */
 } rt_options;
 
 #define RT_HOST_STORE_AUTO   0

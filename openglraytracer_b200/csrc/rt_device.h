@@ -30,6 +30,8 @@
 
 /* from this many hot objects the large-scene kernels put the packet (cone) tests in front of the per-ray loops */
 #define RT_PACKET_MIN_OBJECTS 96
+/* from this many hot objects the CTA-level packet tests (rt_kernel_block.cuh) pay for their barriers */
+#define RT_BLOCK_MIN_OBJECTS 32768
 
 /* Cold record: 64 words. */
 struct RtCold {
@@ -101,6 +103,7 @@ struct RtParams {
     float amb_sum[4];           /* sum of the lights' ambient terms, in light order (glsl:801) */
     int32_t cull;               /* 1: large-scene kernels run the slab test behind the bounding-sphere test */
     int32_t packet;             /* 1: coherent packets (primary rays, shadow rays per light) run the cone test first */
+    int32_t block;              /* 1: CTA-level packet tests (blocks of 2 x 4 work items share the pass over the scene) */
     const float* extent;        /* scene extent E (max |centre| + radius over objects and lights), written by the prologue */
 };
 

@@ -503,6 +503,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     // Packet (cone) tests in front of the per-ray bounding tests; the per-light records are then only a
     // fallback for incoherent packets and are left out (they would halve the resident capacity).
     P.packet = (P.cull && !(o.no_cull & 4) && c->n_box + c->n_sph >= RT_PACKET_MIN_OBJECTS) ? 1 : 0;
+    P.block = (P.packet && !(o.no_cull & 8) && (c->n_box + c->n_sph >= RT_BLOCK_MIN_OBJECTS || (o.no_cull & 16))) ? 1 : 0;
     P.extent = reinterpret_cast<const float*>(c->d_extent.p);
     P.n_lit = (P.cull && !P.packet && !(o.no_cull & 2)) ? c->n_lit : 0;
     P.n_lit_batch = c->n_lit_total <= 3 ? c->n_lit_total : -1;

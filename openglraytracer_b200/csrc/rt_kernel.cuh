@@ -837,30 +837,112 @@ __device__ __forceinline__ float packet_radius(float w, bool sph, float grow, fl
     return __fmaf_rn(rp, 1.000001f, grow);
 }
 
-// The whole object loop for one packet of 3 rays per lane with a common origin `o` per lane: the
-// primary rays of a work item (closest hit: live_min = smallest positive float, glsl:753-776) or the
-// shadow rays of the warp's hit points (any hit below t = 1: live_min = 1, glsl:816).  One copy in the
-// instruction stream for both (out of line, runtime switches): with 16 warps per SM in different
-// phases of a frame the large-scene kernels are instruction-cache bound, not issue bound.
+// The three rays of a lane going through the candidate tests.
+struct RaySet {
+    V3 o[kShadowBatch], d[kShadowBatch];
+    float best[kShadowBatch];
+    int bidx[kShadowBatch];
+    float qe[kShadowBatch];           // |d|^2 * 0.9999 for the bounding test
+    RayQ q[kShadowBatch];
+};
+__device__ __forceinline__ void rayset_load(RaySet& rs, const V3* __restrict__ o_in, const V3* __restrict__ d_in,
+                                            const float* __restrict__ best_in, const int* __restrict__ bidx_in) {
+#pragma unroll
+    for (int r = 0; r < kShadowBatch; ++r) {
+        rs.o[r] = o_in[r]; rs.d[r] = d_in[r]; rs.best[r] = best_in[r]; rs.bidx[r] = bidx_in[r];
+        rs.q[r] = ray_q(rs.d[r]);
+        rs.qe[r] = __fmul_rn(rs.q[r].qa, 0.9999f);
+    }
+}
+// original object index of a hot-list position (boxes 0..n_box-1, then spheres)
+__device__ __forceinline__ int hot_object(const RtParams& P, int hot) {
+    return hot < P.n_box ? __ldg(P.box_obj + hot) : __ldg(P.sph_obj + (hot - P.n_box));
+}
+// One candidate object (hot-list position `hot`, bounding record cc) against the warp's rays: per-ray
+// bounding-sphere test, then the exact test behind a warp vote (the slow paths of boxes_tile_cull /
+// spheres_tile).  Accept rule: smaller t wins; on an exact tie the lower ORIGINAL object index wins.
+// That is what visiting the objects in index order with a strict '<' gives (glsl:744-776), written so
+// that the outcome does not depend on the order the candidates arrive in.
+//   shared (warp-uniform): the three rays of a lane start at one point, one origin transform
+//   want: ray slots this candidate is relevant for (bit r); others are skipped
+template <bool COUNT>
+__device__ __forceinline__ void candidate_test(const RtParams& P, RaySet& rs, int hot, float4 cc, bool shared, float live_min,
+                                               unsigned want, RtCounters& cnt) {
+    constexpr int R = kShadowBatch;
+    const bool anyhit = live_min >= 1.0f;
+    SphO so;
+    if (hot < P.n_box) {
+        unsigned m = 0u;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (r == 0 || !shared) so = sphere_origin(cc, rs.o[r]);
+            const bool live = rs.best[r] >= live_min && ((want >> r) & 1u);
+            if (COUNT) cnt.cull_tests += live;
+            const float hb = __fmaf_rn(rs.d[r].x, so.oc.x, __fmaf_rn(rs.d[r].y, so.oc.y, __fmul_rn(rs.d[r].z, so.oc.z)));
+            const float disc = __fmaf_rn(hb, hb, -__fmul_rn(rs.qe[r], so.qc));
+            if (live && disc >= 0.0f) m |= 1u << r;
+        }
+        if (!__any_sync(kFull, m != 0u)) return;
+        const float4* __restrict__ g = P.box_hot + (size_t)hot * RT_BOX_F4;
+        float4 rec[RT_BOX_F4];
+#pragma unroll
+        for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = __ldg(g + k);
+        V3 bo;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool mine = (m >> r) & 1u;
+            if (r == 0 || !shared) bo = box_origin(rec, rs.o[r]);
+            if (!__any_sync(kFull, mine)) continue;       // warp-uniform: no lane wants this ray slot tested
+            if (COUNT) cnt.box_tests += mine;
+            float tn, tf; Slabs sl; V3 ld;
+            box_slabs(rec, bo, rs.d[r], tn, tf, sl, ld);
+            const float tt = box_pick(tn, tf);
+            // `mine` keeps the outcome a function of the ray alone (not of which lanes share its warp)
+            if (mine && !box_reject(tn, tf) && tt > 0.0f) {
+                if (tt < rs.best[r]) { rs.best[r] = tt; rs.bidx[r] = hot; }
+                else if (!anyhit && tt == rs.best[r] && rs.bidx[r] >= 0 && hot_object(P, hot) < hot_object(P, rs.bidx[r])) rs.bidx[r] = hot;
+            }
+        }
+    } else {
+        // the discriminant of glsl:591, then the roots, ray slot by ray slot
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if (r == 0 || !shared) so = sphere_origin(cc, rs.o[r]);
+            const bool live = rs.best[r] >= live_min && ((want >> r) & 1u);
+            if (COUNT) cnt.cull_tests += live;
+            const float hb = __fmaf_rn(rs.d[r].x, so.oc.x, __fmaf_rn(rs.d[r].y, so.oc.y, __fmul_rn(rs.d[r].z, so.oc.z)));
+            const float disc = __fmaf_rn(hb, hb, -__fmul_rn(rs.q[r].qa, so.qc));
+            const bool go = live && disc >= 0.0f;
+            if (!__any_sync(kFull, go)) continue;
+            if (COUNT) cnt.sphere_tests += go;
+            const float sq = sqrt_approx(fmaxf(disc, 0.0f));
+            const float tn = __fmul_rn(-hb - sq, rs.q[r].iqa);
+            const float tf = __fmul_rn(sq - hb, rs.q[r].iqa);
+            const float tt = (disc < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
+            if (go && tt > 0.0f) {
+                if (tt < rs.best[r]) { rs.best[r] = tt; rs.bidx[r] = hot; }
+                else if (!anyhit && tt == rs.best[r] && rs.bidx[r] >= 0 && hot_object(P, hot) < hot_object(P, rs.bidx[r])) rs.bidx[r] = hot;
+            }
+        }
+    }
+}
+
+// The whole object loop for one packet of 3 rays per lane: the primary rays of a work item (closest
+// hit: live_min = smallest positive float, glsl:753-776) or shadow rays of the warp's hit points (any hit
+// below t = 1: live_min = 1, glsl:816).  One copy in the instruction stream for both (out of line,
+// runtime switches): with 16 warps per SM in different phases of a frame the large-scene kernels are
+// instruction-cache bound, not issue bound.
 template <bool SMEM, bool COUNT, int NC>
 __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
                                           float grow, float live_min, float pad1, float pad2, bool shared, const V3* __restrict__ o_in,
                                           const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
                                           RtCounters& cnt) {
     constexpr int R = kShadowBatch;
-    V3 o[R], d[R];
-    float best[R]; int bidx[R];
+    RaySet rs;
+    rayset_load(rs, o_in, d_in, best_io, bidx_io);
     Cone cone[NC];
-    float qe[R];
-    RayQ q[R];
 #pragma unroll
     for (int k = 0; k < NC; ++k) cone[k] = cone_in[k];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        o[r] = o_in[r]; d[r] = d_in[r]; best[r] = best_io[r]; bidx[r] = bidx_io[r];
-        q[r] = ray_q(d[r]);
-        qe[r] = __fmul_rn(q[r].qa, 0.9999f);
-    }
     const bool anyhit = live_min >= 1.0f;
     const int lane = w.lane;
     // resident: each list is one "tile" in shared memory; streaming: kTileSph-record tiles through the warp's double buffer
@@ -868,13 +950,14 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
     const int n_tiles = nbt + (SMEM ? 1 : n_sph_tiles(P));
     for (int t = 0; t < n_tiles; ++t) {
         // no live ray left in the warp (shadow rays: every one occluded, glsl:816 needs ANY occluder)
-        if (!__any_sync(kFull, best[0] >= live_min || best[1] >= live_min || best[2] >= live_min)) {
+        if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) {
             if (t > 0) tile_drain<SMEM>(w, t - 1, n_tiles);
             break;
         }
         const bool sph = t >= nbt;
         const int base = SMEM ? 0 : (sph ? t - nbt : t) * kTileSph;
         const int n = SMEM ? (sph ? P.n_sph : P.n_box) : min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
+        const int hot0 = (sph ? P.n_box : 0) + base;
         uint32_t ra;
         if (SMEM) {
             ra = smem_addr(smem_f4 + (sph ? w.sph_off4 : w.box_off4));
@@ -891,7 +974,7 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
         for (int i0 = 0; i0 < n; i0 += 32 * kHalves) {
             // shadow packets: leave as soon as every ray of the warp is occluded (checked every 256 objects)
             if (anyhit && (i0 & 255) == 0 && i0 > 0 &&
-                !__any_sync(kFull, best[0] >= 1.0f || best[1] >= 1.0f || best[2] >= 1.0f)) break;
+                !__any_sync(kFull, rs.best[0] >= 1.0f || rs.best[1] >= 1.0f || rs.best[2] >= 1.0f)) break;
             const int j0 = i0 + lane, j1 = j0 + 32;
             const float4 c0 = lds128(ra + (uint32_t)min(j0, n - 1) * 16u);
             const float rp0 = packet_radius(c0.w, sph, grow, pad1, pad2);
@@ -915,74 +998,19 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
             if ((mask0 | mask1) == 0u) continue;
 #pragma unroll 1
             for (int half = 0; half < kHalves; ++half) {
-            unsigned mask = half ? mask1 : mask0;
-            const int i = i0 + 32 * half;
-            while (mask) {
-                const int idx = i + __ffs(mask) - 1;
-                mask &= mask - 1u;
-                const float4 cc = lds128(ra + (uint32_t)idx * 16u);
-                if (!sph) {
-                    // per-ray bounding-sphere test, then the slab test (the slow path of boxes_tile_cull);
-                    // `shared` (warp-uniform): the three rays of a lane start at one point, one origin transform
-                    unsigned m = 0u;
-                    SphO so;
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        if (r == 0 || !shared) so = sphere_origin(cc, o[r]);
-                        const bool live = best[r] >= live_min;
-                        if (COUNT) cnt.cull_tests += live;
-                        const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
-                        const float disc = __fmaf_rn(hb, hb, -__fmul_rn(qe[r], so.qc));
-                        if (live && disc >= 0.0f) m |= 1u << r;
-                    }
-                    if (__any_sync(kFull, m != 0u)) {
-                        const float4* __restrict__ g = P.box_hot + (size_t)(base + idx) * RT_BOX_F4;
-                        float4 rec[RT_BOX_F4];
-#pragma unroll
-                        for (int k = 0; k < RT_BOX_F4; ++k) rec[k] = __ldg(g + k);
-                        V3 bo;
-#pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            const bool mine = (m >> r) & 1u;
-                            if (r == 0 || !shared) bo = box_origin(rec, o[r]);
-                            if (!__any_sync(kFull, mine)) continue;       // warp-uniform: no lane wants this ray slot tested
-                            if (COUNT) cnt.box_tests += mine;
-                            float tn, tf; Slabs sl; V3 ld;
-                            box_slabs(rec, bo, d[r], tn, tf, sl, ld);
-                            const float tt = box_pick(tn, tf);
-                            // `mine` keeps the outcome a function of the ray alone (not of which lanes share its warp)
-                            if (mine && !box_reject(tn, tf) && tt > 0.0f && tt < best[r]) { best[r] = tt; bidx[r] = base + idx; }
-                        }
-                    }
-                } else {
-                    // the discriminant of glsl:591, then the roots (the slow path of spheres_tile), ray slot by ray slot
-#pragma unroll
-                    SphO so;
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        if (r == 0 || !shared) so = sphere_origin(cc, o[r]);
-                        const bool live = best[r] >= live_min;
-                        if (COUNT) cnt.cull_tests += live;
-                        const float hb = __fmaf_rn(d[r].x, so.oc.x, __fmaf_rn(d[r].y, so.oc.y, __fmul_rn(d[r].z, so.oc.z)));
-                        const float disc = __fmaf_rn(hb, hb, -__fmul_rn(q[r].qa, so.qc));
-                        if (!__any_sync(kFull, live && disc >= 0.0f)) continue;
-                        if (COUNT) cnt.sphere_tests += live && disc >= 0.0f;
-                        const float sq = sqrt_approx(fmaxf(disc, 0.0f));
-                        const float tn = __fmul_rn(-hb - sq, q[r].iqa);
-                        const float tf = __fmul_rn(sq - hb, q[r].iqa);
-                        const float tt = (disc < 0.0f) ? -1.0f : ((tn < 0.0f) ? tf : tn);
-                        if (tt > 0.0f && tt < best[r]) { best[r] = tt; bidx[r] = P.n_box + base + idx; }
-                        else if (!anyhit && tt == best[r] && bidx[r] >= 0 && bidx[r] < P.n_box) {
-                            if (__ldg(P.sph_obj + base + idx) < __ldg(P.box_obj + bidx[r])) bidx[r] = P.n_box + base + idx;
-                        }
-                    }
+                unsigned mask = half ? mask1 : mask0;
+                const int i = i0 + 32 * half;
+                while (mask) {
+                    const int idx = i + __ffs(mask) - 1;
+                    mask &= mask - 1u;
+                    const float4 cc = lds128(ra + (uint32_t)idx * 16u);
+                    candidate_test<COUNT>(P, rs, hot0 + idx, cc, shared, live_min, 7u, cnt);
                 }
-            }
             }
         }
     }
 #pragma unroll
-    for (int r = 0; r < R; ++r) { best_io[r] = best[r]; bidx_io[r] = bidx[r]; }
+    for (int r = 0; r < R; ++r) { best_io[r] = rs.best[r]; bidx_io[r] = rs.bidx[r]; }
 }
 
 // One tile, dispatched on its kind.
@@ -1827,6 +1855,10 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
         }
     }
 }
+
+#if !RT_STRICT
+#include "rt_kernel_block.cuh"
+#endif
 
 }  // namespace RT_NS
 

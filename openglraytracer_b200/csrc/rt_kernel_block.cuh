@@ -1,0 +1,481 @@
+/*
+ * rt_kernel_block.cuh — the large-scene kernel with CTA-level packet tests (included by rt_kernel.cuh,
+ * fast kernel only, inside namespace rt_fast).
+ *
+ * render_kernel<.., CULL> lets every warp test every object against the cone of its own work item
+ * (packet_trace).  Here the 8 warps of a CTA take a BLOCK of 2 x 4 work items (48 x 16 pixels) and
+ * share that pass: all 256 threads test the scene, one object per thread and trip, against the cone of
+ * the whole block (primary rays: around the block's corner rays, glsl:377-392; shadow rays: per lit
+ * light, around the block's hit points seen from the light, glsl:808-809) and append the objects that
+ * meet it to a list in shared memory.  Each warp then runs its own cone test and the per-ray tests
+ * (candidate_test) over that list only.  Every object is still tested for every block -- no hierarchy
+ * over the scene, no sorting -- but the pass over the N objects is paid once per 8 work items.
+ *
+ * The list is unordered (warps append concurrently); candidate_test's accept rule (smaller t, then lower
+ * original object index) makes the result independent of the order, so frames stay byte-identical to
+ * the per-warp path and to the plain loops (tests/test_gpu_parity.py).
+ *
+ * Barriers: every __syncthreads() below sits in CTA-uniform control flow (conditions on kernel
+ * parameters or on values read from shared memory after a barrier), never under a per-warp condition.
+ */
+#pragma once
+
+constexpr int kBlkW = 2, kBlkH = 4;              // work items per block
+constexpr int kListCap = 2048;                   // primary candidates per block; an overflowing block falls back to packet_trace
+constexpr int kListCapB = 2048;                  // shadow candidates per block (up to three lights)
+constexpr float kBlockMinCos = kConeMinCos;      // wider block cones: the block falls back to packet_trace
+
+struct BlockShared {
+    uint32_t list_a[kListCap];                   // primary candidates of the block: hot index | 1 << 28
+    uint32_t list_b[kListCapB];                  // shadow candidates: hot index | lit-light mask << 28
+    float sum[kWarps][12];                       // per warp, per light slot: sum of unit directions (xyz), count
+    float mx[kWarps][12];                        // per warp, per light slot: max sin^2, max |L - p|^2, in-cone flag
+    unsigned count_a, count_b[2];                // count_b: one per sample parity (reset while the other is in use)
+    unsigned pad_;
+    unsigned long long next;
+};
+constexpr int kBlockSharedBytes = (int)((sizeof(BlockShared) + 15) / 16 * 16);
+
+// All threads of the CTA: one object per thread and trip against NC cones; hits are appended to `list`.
+template <bool SMEM, bool COUNT, int NC>
+__device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w, const Cone (&cone)[NC], unsigned on,
+                                             float grow, float pad1, float pad2, uint32_t* __restrict__ list, int cap,
+                                             unsigned* __restrict__ counter, RtCounters& cnt) {
+    const int n_hot = P.n_box + P.n_sph;
+    const unsigned lt_mask = (1u << w.lane) - 1u;
+    constexpr int B = 4;                          // records in flight per thread (L2 latency when streaming)
+    for (int j0 = 0; j0 < n_hot; j0 += kThreads * B) {
+        float4 c[B];
+        int jj[B];
+#pragma unroll
+        for (int b = 0; b < B; ++b) {
+            jj[b] = j0 + b * kThreads + (int)threadIdx.x;
+            const int idx = min(jj[b], n_hot - 1);
+            const bool sph = idx >= P.n_box;
+            if (SMEM) c[b] = smem_f4[sph ? w.sph_off4 + (uint32_t)(idx - P.n_box) : w.box_off4 + (uint32_t)idx];
+            else c[b] = sph ? __ldg(P.sph_hot + (idx - P.n_box)) : __ldg(P.box_cull + idx);
+        }
+#pragma unroll
+        for (int b = 0; b < B; ++b) {
+            if (j0 + b * kThreads >= n_hot) break;                 // CTA-uniform
+            const bool in = jj[b] < n_hot;
+            const bool sph = min(jj[b], n_hot - 1) >= P.n_box;
+            const float rp = packet_radius(c[b].w, sph, grow, pad1, pad2);
+            unsigned cm = 0u;
+#pragma unroll
+            for (int k = 0; k < NC; ++k)
+                if (NC == 1 || ((on >> k) & 1u)) cm |= cone_pass(cone[k], c[b], rp) ? (1u << k) : 0u;
+            if (!in) cm = 0u;
+            if (COUNT && in) cnt.packet_tests += (unsigned long long)(NC == 1 ? 1 : __popc(on));
+            const unsigned mask = __ballot_sync(kFull, cm != 0u);
+            if (mask) {
+                unsigned base = 0u;
+                if (w.lane == 0) base = atomicAdd(counter, (unsigned)__popc(mask));
+                base = __shfl_sync(kFull, base, 0);
+                const unsigned pos = base + (unsigned)__popc(mask & lt_mask);
+                if (cm != 0u && pos < (unsigned)cap) list[pos] = (uint32_t)jj[b] | (cm << 28);
+            }
+        }
+    }
+}
+
+// One warp: its 3 rays per lane against the entries of a block list whose mask has bit `kbit`; the
+// warp's own cone first (one entry per lane), then candidate_test for the survivors.
+template <bool SMEM, bool COUNT>
+__device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, const uint32_t* __restrict__ list, int count, unsigned kbit,
+                                        const Cone* __restrict__ cone_in, bool use_cone, float grow, float live_min, float pad1, float pad2,
+                                        bool shared, const V3* __restrict__ o_in, const V3* __restrict__ d_in,
+                                        float* __restrict__ best_io, int* __restrict__ bidx_io, RtCounters& cnt) {
+    RaySet rs;
+    rayset_load(rs, o_in, d_in, best_io, bidx_io);
+    const Cone cone = cone_in[0];
+    const int lane = w.lane;
+    for (int e0 = 0; e0 < count; e0 += 32) {
+        if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
+        const int e = e0 + lane;
+        const uint32_t ent = e < count ? list[e] : 0u;
+        const int hot = (int)(ent & 0x0fffffffu);
+        const bool sel = e < count && ((ent >> 28) & kbit) != 0u;
+        const bool sph = hot >= P.n_box;
+        float4 c;
+        if (SMEM) c = smem_f4[sph ? w.sph_off4 + (uint32_t)(hot - P.n_box) : w.box_off4 + (uint32_t)hot];
+        else c = sph ? __ldg(P.sph_hot + (hot - P.n_box)) : __ldg(P.box_cull + hot);
+        const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
+        const bool pass = sel && (!use_cone || cone_pass(cone, c, rp));     // a wide warp cone: every selected entry goes on
+        if (COUNT) cnt.packet_tests += sel;
+        unsigned mask = __ballot_sync(kFull, pass);
+        while (mask) {
+            const int src = __ffs(mask) - 1;
+            mask &= mask - 1u;
+            const int hot_s = __shfl_sync(kFull, hot, src);
+            const float4 cc = make_float4(__shfl_sync(kFull, c.x, src), __shfl_sync(kFull, c.y, src),
+                                          __shfl_sync(kFull, c.z, src), __shfl_sync(kFull, c.w, src));
+            candidate_test<COUNT>(P, rs, hot_s, cc, shared, live_min, 7u, cnt);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < kShadowBatch; ++r) { best_io[r] = rs.best[r]; bidx_io[r] = rs.bidx[r]; }
+}
+
+template <bool SMEM, bool COUNT>
+__global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_kernel(const __grid_constant__ RtParams P) {
+    constexpr bool CULL = true, REPACK = true;
+    constexpr int NP = kShadowBatch;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpCtx w;
+    w.lane = lane;
+    w.phase = 0u;
+    size_t off4 = 0;                         // in float4 units; layout as in render_kernel, then BlockShared
+    if (SMEM) {
+        const int nb4 = P.n_box, ns4 = P.n_sph;
+        for (int i = threadIdx.x; i < nb4; i += kThreads) smem_f4[i] = __ldg(P.box_cull + i);
+        for (int i = threadIdx.x; i < ns4; i += kThreads) smem_f4[nb4 + i] = __ldg(P.sph_hot + i);
+        w.box_off4 = 0u;
+        w.sph_off4 = (uint32_t)nb4;
+        off4 = (size_t)nb4 + ns4;
+        w.lrec_off4 = (uint32_t)off4;
+    } else {
+        w.box_off4 = w.sph_off4 = w.lrec_off4 = 0u;
+    }
+    {
+        float4* scratch = smem_f4 + off4 + (size_t)warp * (kScratchBytes / 16);
+        w.queue = reinterpret_cast<float*>(scratch);
+        w.occ = reinterpret_cast<int*>(scratch + kQueueRays * 2);
+        off4 += (size_t)kWarps * (kScratchBytes / 16);
+    }
+    w.buf_off4[0] = w.buf_off4[1] = 0u;
+    w.buf_addr[0] = w.buf_addr[1] = w.bar_addr[0] = w.bar_addr[1] = 0u;
+    if (!SMEM) {
+        w.buf_off4[0] = (uint32_t)(off4 + (size_t)warp * (2 * kTileBytes / 16));
+        w.buf_off4[1] = w.buf_off4[0] + kTileBytes / 16;
+        off4 += (size_t)kWarps * (2 * kTileBytes / 16);
+        uint64_t* bars = reinterpret_cast<uint64_t*>(smem_f4 + off4) + warp * 2;
+        off4 += (size_t)kWarps;               // 16 bytes of barriers per warp
+        w.buf_addr[0] = smem_addr(smem_f4 + w.buf_off4[0]); w.buf_addr[1] = smem_addr(smem_f4 + w.buf_off4[1]);
+        w.bar_addr[0] = smem_addr(bars); w.bar_addr[1] = smem_addr(bars + 1);
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(w.bar_addr[0]) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(w.bar_addr[1]) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
+    BlockShared* bs = reinterpret_cast<BlockShared*>(smem_f4 + off4);
+    if (threadIdx.x == 0) { bs->count_a = 0u; bs->count_b[0] = 0u; bs->count_b[1] = 0u; }
+    __syncthreads();
+
+    const int lx = lane & 7, ly = lane >> 3;
+    const float E = __ldg(P.extent);
+    const float pk_pad1 = 2e-6f * E, pk_pad2 = 4e-6f * E * E;
+    const int bx_n = (P.tiles_x + kBlkW - 1) / kBlkW, by_n = (P.tiles_y + kBlkH - 1) / kBlkH;
+    const long long blocks_per_frame = (long long)bx_n * by_n;
+    const long long n_blocks = blocks_per_frame * P.n_frames;
+    const int n_lights_b = (P.n_lit_batch > 0 && P.n_lit_batch <= kShadowBatch) ? P.n_lit_batch : 0;    // CTA-uniform
+
+    RtCounters cnt;
+    cnt.packet_tests = 0ull;
+    cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
+    cnt.cull_tests = cnt.warp_iters = 0ull;
+
+    for (long long blk = blockIdx.x; blk < n_blocks;) {
+        const int frame = (int)(blk / blocks_per_frame);
+        const int bin = (int)(blk - (long long)frame * blocks_per_frame);
+        const int by = bin / bx_n, bx = bin - by * bx_n;
+        const int tx = bx * kBlkW + (warp & (kBlkW - 1)), ty = by * kBlkH + (warp / kBlkW);     // this warp's work item
+        const bool item_ok = tx < P.tiles_x && ty < P.tiles_y;
+        const int py = P.y0 + ty * 4 + ly;
+        int px[NP]; bool valid[NP];
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            px[q] = (tx * NP + q) * 8 + lx;
+            valid[q] = item_ok && px[q] < P.width && py < P.y1;
+        }
+        const RtCameraDev* __restrict__ cam = P.cams + frame;
+        const V3 org = mk(cam->position[0], cam->position[1], cam->position[2]);   // glsl:391
+
+        // ---- the block's primary cone: axis through the middle of its 48 x 16 pixels, half-angle from its corner
+        // rays (the angle to the axis is quasi-convex on the image plane, so a corner attains the maximum)
+        Cone bc[1];
+        bool a_ok;
+        {
+            const int x0 = bx * kBlkW * 8 * NP, yb = P.y0 + by * kBlkH * 4;
+            bc[0].apex = org;
+            bc[0].axis = primary_dir(P, cam, x0 + kBlkW * 4 * NP, yb + kBlkH * 2, 0.0f, 0.0f);
+            const V3 cd = primary_dir(P, cam, x0 + (lane & 1) * kBlkW * 8 * NP, yb + ((lane >> 1) & 1) * kBlkH * 4, 0.0f, 0.0f);
+            const V3 x = cross3(bc[0].axis, cd);
+            const float s2 = fminf(__fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z))), 1.0f);
+            a_ok = __all_sync(kFull, dot3(bc[0].axis, cd) >= kBlockMinCos);       // same inputs in every warp: CTA-uniform
+            cone_close(bc[0], warp_max_nonneg(s2), kFar * 1.001f);
+        }
+        if (a_ok) block_filter<SMEM, COUNT, 1>(P, w, bc, 1u, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
+        __syncthreads();                                                        // list A complete
+        const int na = (int)bs->count_a;
+        const bool use_a = a_ok && na <= kListCap;
+
+        V3 sum[NP];
+#pragma unroll
+        for (int q = 0; q < NP; ++q) sum[q] = mk(0.0f, 0.0f, 0.0f);
+        for (int s = 0; s < P.spp; ++s) {
+            V3 dir[kShadowBatch];
+#pragma unroll
+            for (int q = 0; q < NP; ++q) {
+                float jx, jy;
+                jitter(P, px[q], py, s, jx, jy);
+                dir[q] = primary_dir(P, cam, px[q], py, jx, jy);
+            }
+            // PHASE 0 of the three root frames (glsl:956-967): the warp's own cone, then the block list
+            V3 o3[kShadowBatch];
+            float best[kShadowBatch]; int bidx[kShadowBatch];
+#pragma unroll
+            for (int q = 0; q < kShadowBatch; ++q) { o3[q] = org; bidx[q] = -1; best[q] = valid[q] ? kFar : 0.0f; }
+            Cone pc[1];
+            bool packet;
+            {
+                pc[0].apex = org;
+                pc[0].axis = primary_dir(P, cam, tx * (8 * NP) + 4 * NP, P.y0 + ty * 4 + 2, 0.0f, 0.0f);
+                float s2 = 0.0f;
+                bool in_cone = true;
+#pragma unroll
+                for (int q = 0; q < kShadowBatch; ++q) {
+                    const V3 x = cross3(pc[0].axis, dir[q]);
+                    const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+                    if (valid[q]) {
+                        s2 = fmaxf(s2, fminf(s2q, 1.0f));
+                        in_cone = in_cone && dot3(pc[0].axis, dir[q]) >= kConeMinCos;
+                    }
+                }
+                packet = __all_sync(kFull, in_cone);
+                cone_close(pc[0], warp_max_nonneg(s2), kFar * 1.001f);
+            }
+            if (packet && use_a) {
+                list_trace<SMEM, COUNT>(P, w, bs->list_a, na, 1u, pc, true, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
+            } else if (packet) {
+                packet_trace<SMEM, COUNT, 1>(P, w, pc, 1u, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
+            } else {
+                const int n_obj_tiles = n_box_tiles<CULL>(P) + n_sph_tiles(P);
+                tile_begin<SMEM, CULL>(P, w);
+                for (int t = 0; t < n_obj_tiles; ++t) {
+                    const float4* recs = tile_acquire<SMEM, CULL>(P, w, t, n_obj_tiles);
+                    any_tile<kShadowBatch, false, true, COUNT, CULL>(P, recs, t, o3, dir, best, bidx, cnt);
+                }
+            }
+
+            // ---- root hits: hit point, shadow-ray origin and "needs shading" exactly as trace_sample builds them
+            bool have_sb = false;
+            float rsb[kShadowBatch][kShadowBatch];       // [tile q][light slot]
+#pragma unroll
+            for (int q = 0; q < kShadowBatch; ++q)
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) rsb[q][k] = 0.0f;
+            if (n_lights_b > 0) {                        // CTA-uniform
+                V3 hp[kShadowBatch], so3[kShadowBatch];
+                bool sh[kShadowBatch];
+#pragma unroll 1
+                for (int q = 0; q < kShadowBatch; ++q) {
+                    const V3 dq = q == 0 ? dir[0] : (q == 1 ? dir[1] : dir[2]);
+                    const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
+                    const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
+                    const bool vq = q == 0 ? valid[0] : (q == 1 ? valid[1] : valid[2]);
+                    bool shade = false;
+                    V3 p = mk(0.0f, 0.0f, 0.0f), so = mk(0.0f, 0.0f, 0.0f);
+                    if (vq && iq >= 0) {
+                        const Hit h = resolve_hit<SMEM, CULL>(P, w, org, dq, tq, iq);
+                        const RtCold* __restrict__ mat = P.cold + h.obj;
+                        float wp = 1.0f;                 // the weight of the Phong term at the root node
+                        if (P.max_depth > 0 && mat->reflectivity > 0.0f) wp = wp * (1.0f - mat->reflectivity);
+                        if (P.max_depth > 0 && mat->transparency > 0.0f) wp = wp * (1.0f - mat->transparency);
+                        shade = wp != 0.0f;
+                        p = h.p;
+                        so = h.p + h.n * 0.01f;                                            // glsl:808
+                    }
+                    if (q == 0) { hp[0] = p; so3[0] = so; sh[0] = shade; }
+                    else if (q == 1) { hp[1] = p; so3[1] = so; sh[1] = shade; }
+                    else { hp[2] = p; so3[2] = so; sh[2] = shade; }
+                }
+                // ---- the block's light cones: sum of the unit directions light -> hit point over the CTA ...
+                V3 lp[kShadowBatch];
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) {
+                    const RtLightDev* __restrict__ L = P.lights + P.lit[k < n_lights_b ? k : 0];
+                    lp[k] = mk(L->position[0], L->position[1], L->position[2]);
+                }
+                V3 u[kShadowBatch][kShadowBatch];        // [light][tile]
+                float l2[kShadowBatch][kShadowBatch];
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) {
+                    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                    for (int q = 0; q < kShadowBatch; ++q) {
+                        const V3 v = hp[q] - lp[k];
+                        l2[k][q] = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
+                        u[k][q] = v * rsqrtf(l2[k][q]);
+                        if (sh[q] && k < n_lights_b) { acc[0] += u[k][q].x; acc[1] += u[k][q].y; acc[2] += u[k][q].z; acc[3] += 1.0f; }
+                    }
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+                        for (int c4 = 0; c4 < 4; ++c4) acc[c4] += __shfl_xor_sync(kFull, acc[c4], off);
+                    }
+                    if (lane == 0) {
+#pragma unroll
+                        for (int c4 = 0; c4 < 4; ++c4) bs->sum[warp][4 * k + c4] = acc[c4];
+                    }
+                }
+                __syncthreads();                                                    // sums visible
+                Cone lc[kShadowBatch];
+                unsigned on = 0u;
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) {
+                    float t4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                    for (int ww = 0; ww < kWarps; ++ww) {
+#pragma unroll
+                        for (int c4 = 0; c4 < 4; ++c4) t4[c4] += bs->sum[ww][4 * k + c4];
+                    }
+                    lc[k].apex = lp[k];
+                    lc[k].axis = normalize3(mk(t4[0], t4[1], t4[2]));
+                    if (k < n_lights_b && t4[3] > 0.0f) on |= 1u << k;
+                    // ... then the half-angle, the reach and "all inside kConeMinCos" over the CTA
+                    float s2 = 0.0f, lmax = 0.0f;
+                    bool in_cone = true;
+#pragma unroll
+                    for (int q = 0; q < kShadowBatch; ++q) {
+                        const V3 x = cross3(lc[k].axis, u[k][q]);
+                        const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+                        if (sh[q]) {
+                            s2 = fmaxf(s2, fminf(s2q, 1.0f));
+                            lmax = fmaxf(lmax, l2[k][q]);
+                            in_cone = in_cone && dot3(lc[k].axis, u[k][q]) >= kBlockMinCos;    // NaN -> false
+                        }
+                    }
+                    const float s2w = warp_max_nonneg(s2), lw = warp_max_nonneg(lmax);
+                    const bool okw = __all_sync(kFull, in_cone);
+                    if (lane == 0) { bs->mx[warp][4 * k] = s2w; bs->mx[warp][4 * k + 1] = lw; bs->mx[warp][4 * k + 2] = okw ? 1.0f : 0.0f; }
+                }
+                __syncthreads();                                                    // maxima visible
+                bool b_ok = true;
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) {
+                    float s2 = 0.0f, lmax = 0.0f;
+                    for (int ww = 0; ww < kWarps; ++ww) {
+                        s2 = fmaxf(s2, bs->mx[ww][4 * k]);
+                        lmax = fmaxf(lmax, bs->mx[ww][4 * k + 1]);
+                        if ((on >> k) & 1u) b_ok = b_ok && bs->mx[ww][4 * k + 2] != 0.0f;
+                    }
+                    cone_close(lc[k], s2, __fmaf_rn(sqrt_approx(lmax), 1.0001f, 0.0101f));
+                }
+                // every thread holds the same `on`, `b_ok`, cones (all read from shared memory): CTA-uniform
+                if (b_ok && on != 0u)
+                    block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, 0.0101f, pk_pad1, pk_pad2, bs->list_b, kListCapB, &bs->count_b[s & 1], cnt);
+                __syncthreads();                                                    // list B complete
+                const int nb = (int)bs->count_b[s & 1];
+                if (threadIdx.x == 0) bs->count_b[(s + 1) & 1] = 0u;                // its readers (sample s - 1) are past two barriers
+                const bool use_b = b_ok && nb <= kListCapB;
+
+                // ---- this warp's root shadow rays, light by light (one cone over its own 96 hit points)
+                if (packet) {
+                    have_sb = true;
+                    if (__any_sync(kFull, sh[0] || sh[1] || sh[2])) {
+#pragma unroll 1
+                        for (int k = 0; k < n_lights_b; ++k) {
+                            const V3 lpk = k == 0 ? lp[0] : (k == 1 ? lp[1] : lp[2]);
+                            V3 sd3[kShadowBatch], uu[kShadowBatch];
+                            float ll[kShadowBatch], sbk[kShadowBatch];
+                            V3 sm = mk(0.0f, 0.0f, 0.0f);
+#pragma unroll
+                            for (int q = 0; q < kShadowBatch; ++q) {
+                                sd3[q] = sh[q] ? mk(lpk.x - hp[q].x, lpk.y - hp[q].y, lpk.z - hp[q].z) : mk(0.0f, 0.0f, 1.0f);   // glsl:809
+                                sbk[q] = sh[q] ? 1.0f : 0.0f;
+                                ll[q] = __fmaf_rn(sd3[q].x, sd3[q].x, __fmaf_rn(sd3[q].y, sd3[q].y, __fmul_rn(sd3[q].z, sd3[q].z)));
+                                uu[q] = sd3[q] * -rsqrtf(ll[q]);
+                                if (sh[q]) sm = sm + uu[q];
+                            }
+#pragma unroll
+                            for (int off = 16; off > 0; off >>= 1) {
+                                sm.x += __shfl_xor_sync(kFull, sm.x, off);
+                                sm.y += __shfl_xor_sync(kFull, sm.y, off);
+                                sm.z += __shfl_xor_sync(kFull, sm.z, off);
+                            }
+                            Cone wc[1];
+                            wc[0].apex = lpk;
+                            wc[0].axis = normalize3(sm);
+                            float s2 = 0.0f, lmax = 0.0f;
+                            bool in_cone = true;
+#pragma unroll
+                            for (int q = 0; q < kShadowBatch; ++q) {
+                                const V3 x = cross3(wc[0].axis, uu[q]);
+                                const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+                                if (sh[q]) {
+                                    s2 = fmaxf(s2, fminf(s2q, 1.0f));
+                                    lmax = fmaxf(lmax, ll[q]);
+                                    in_cone = in_cone && dot3(wc[0].axis, uu[q]) >= kConeMinCos;
+                                }
+                            }
+                            const bool narrow = __all_sync(kFull, in_cone);
+                            if (!narrow && !use_b) { have_sb = false; break; }                    // wide packet, no list: per tile in trace_sample
+                            cone_close(wc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
+                            int unused[kShadowBatch] = {-1, -1, -1};
+                            if (use_b) list_trace<SMEM, COUNT>(P, w, bs->list_b, nb, 1u << k, wc, narrow, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
+                            else packet_trace<SMEM, COUNT, 1>(P, w, wc, 1u, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
+#pragma unroll
+                            for (int q = 0; q < kShadowBatch; ++q) {
+                                if (k == 0) rsb[q][0] = sbk[q]; else if (k == 1) rsb[q][1] = sbk[q]; else rsb[q][2] = sbk[q];
+                            }
+                        }
+                    }
+                }
+            }
+            // one copy of the bounce machinery in the instruction stream: rolled loop, selected operands
+#pragma unroll 1
+            for (int q = 0; q < NP; ++q) {
+                const V3 dq = q == 0 ? dir[0] : (q == 1 ? dir[1] : dir[2]);
+                const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
+                const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
+                const bool vq = q == 0 ? valid[0] : (q == 1 ? valid[1] : valid[2]);
+                float fsb[kShadowBatch];
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) fsb[k] = q == 0 ? rsb[0][k] : (q == 1 ? rsb[1][k] : rsb[2][k]);
+                const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, have_sb, fsb, pk_pad1, pk_pad2, cnt);
+                if (q == 0) sum[0] = sum[0] + c;
+                else if (q == 1) sum[1] = sum[1] + c;
+                else sum[2] = sum[2] + c;
+            }
+        }
+        uint8_t* frame_out = P.out + (long long)frame * P.frame_stride;
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const float fs = (float)P.spp;
+            const V3 fc = mk(fdiv(sum[q].x, fs), fdiv(sum[q].y, fs), fdiv(sum[q].z, fs));
+            const uint32_t word = unorm8(fc.x) | (unorm8(fc.y) << 8) | (unorm8(fc.z) << 16);      // glsl:404
+            const long long pix = (long long)(py - P.out_row0) * P.width + px[q];
+            const uint32_t w1 = __shfl_down_sync(kFull, word, 1);
+            const uint32_t w2 = __shfl_down_sync(kFull, word, 2);
+            const uint32_t w3 = __shfl_down_sync(kFull, word, 3);
+            const bool vec_ok = ((P.width & 3) == 0) && ((tx * NP + q) * 8 + 8 <= P.width) &&
+                                ((reinterpret_cast<uintptr_t>(frame_out) & 15) == 0);
+            if (vec_ok) {
+                if ((lane & 3) == 0 && item_ok && py < P.y1)
+                    *reinterpret_cast<uint4*>(frame_out + pix * 4) = make_uint4(word, w1, w2, w3);
+            } else if (valid[q]) {
+                *reinterpret_cast<uint32_t*>(frame_out + pix * 4) = word;
+            }
+        }
+        // next block for the whole CTA; list A is reset for it (every warp is past its reads of both lists here
+        // only after the barrier, so the reset sits behind it)
+        if (threadIdx.x == 0) bs->next = (unsigned long long)gridDim.x + atomicAdd(P.tile_counter, 1ull);
+        __syncthreads();
+        blk = (long long)bs->next;
+        if (threadIdx.x == 0) { bs->count_a = 0u; bs->count_b[0] = 0u; bs->count_b[1] = 0u; }
+        __syncthreads();
+    }
+
+    if (COUNT) {
+        if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
+        unsigned long long v[11] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests};
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+            unsigned long long x = v[k];
+            for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
+            if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);
+        }
+    }
+}

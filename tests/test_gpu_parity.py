@@ -198,6 +198,13 @@ def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
     # bit 2: no packet (cone) tests -> per-ray bounding tests with per-light shadow records; bit 1: without them
     assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=4))
     assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=6))
+    # bit 4: CTA-level packet tests (blocks of 2 x 4 work items share the pass over the scene; unordered
+    # candidate lists) forced on below their object-count threshold; bit 3: off
+    blk, st_blk = tracer.render(sc, cam, w, h, want_stats=True, no_cull=16)
+    assert np.array_equal(on, blk)
+    assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=16))
+    assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=8))
+    assert st_blk["rays"] == st_on["rays"] and 0 < st_blk["packet_tests"] < st_on["packet_tests"]
     _, st_ray = tracer.render(sc, cam, w, h, want_stats=True, no_cull=4)
     assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
     assert st_off["cull_tests"] == 0 and st_on["cull_tests"] > 0
@@ -208,6 +215,9 @@ def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
     edges = [0, 37, 90, h]
     for y0, y1 in zip(edges[:-1], edges[1:]):
         canvas[y0:y1] = tracer.render(sc, cam, w, h, y0=y0, y1=y1, band_only=True)
+    assert np.array_equal(canvas, on)
+    for y0, y1 in zip(edges[:-1], edges[1:]):
+        canvas[y0:y1] = tracer.render(sc, cam, w, h, y0=y0, y1=y1, band_only=True, no_cull=16)
     assert np.array_equal(canvas, on)
 
 
@@ -224,6 +234,7 @@ def test_large_scene_kernel_with_spp_and_batch(tracer):
     _check(batch[1], ob.render(sc, cams[1], w, h, spp=4), "scaled 200 spp4 batch frame 1", need_edges=False)
     assert np.array_equal(batch, tracer.render(sc, cams, w, h, spp=4, no_cull=1))
     assert np.array_equal(batch, tracer.render(sc, cams, w, h, spp=4, no_cull=4))
+    assert np.array_equal(batch, tracer.render(sc, cams, w, h, spp=4, no_cull=16))      # block kernel: several samples and frames
     for (ww, hh) in [(1, 1), (23, 5), (25, 4), (49, 3)]:
         img = tracer.render(sc, cams[0], ww, hh)
         rep = compare(img, ob.render(sc, cams[0], ww, hh))
@@ -250,6 +261,7 @@ def test_device_prologue_matches_host_prologue_and_oracle():
             # bands and the bounding-test switch stay byte-identical under the device prologue too
             assert np.array_equal(a, dev.render(sc, cam, w, h, no_cull=1))
             assert np.array_equal(a, dev.render(sc, cam, w, h, no_cull=4))
+            assert np.array_equal(a, dev.render(sc, cam, w, h, no_cull=16))
             top = dev.render(sc, cam, w, h, y0=0, y1=50, band_only=True)
             assert np.array_equal(top, a[:50])
             # a strict render after a device prologue falls back to the host records (op-for-op parity)
@@ -296,7 +308,7 @@ def test_bounding_sphere_test_far_and_tiny_objects(tracer):
     for half in (11.0, 3000.0):
         sc = _far_scene(half)
         on = tracer.render(sc, cam, 320, 180)
-        for mode in (1, 2, 4, 6):
+        for mode in (1, 2, 4, 6, 8, 16):
             assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=mode)), mode
         ref = ob.render(sc, cam, 320, 180)
         _check(tracer.render(sc, cam, 320, 180, strict=True), ref, "far/tiny objects strict", need_edges=False)

@@ -8,7 +8,7 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 w, h = (int(sys.argv[2]), int(sys.argv[3])) if len(sys.argv) > 3 else (1920, 1080)
 depth = int(sys.argv[4]) if len(sys.argv) > 4 else 0
 reps = int(sys.argv[5]) if len(sys.argv) > 5 else 3
-no_cull = {"nocull": 1, "nopacket": 4, "nopacket_nolrec": 6}.get(sys.argv[6], 0) if len(sys.argv) > 6 else 0
+no_cull = {"nocull": 1, "nopacket": 4, "nopacket_nolrec": 6, "noblock": 8, "block": 16}.get(sys.argv[6], 0) if len(sys.argv) > 6 else 0
 sc = rt.scaled_scene(n, max_depth=depth) if n > 5 else rt.builtin_scene(0.0, depth)
 cam = rt.builtin_camera(0.0)
 r = rt.Raytracer()

@@ -16,6 +16,8 @@ for name, sc, w, h, kw in [
         ("scaled 200 nocull", rt.scaled_scene(200, max_depth=1), 72, 40, {"no_cull": 1}),
         ("scaled 200 no lrec", rt.scaled_scene(200, max_depth=1), 72, 40, {"no_cull": 2}),
         ("scaled 200 no packet", rt.scaled_scene(200, max_depth=1), 72, 40, {"no_cull": 4}),
+        ("scaled 200 block kernel", rt.scaled_scene(200, max_depth=1), 72, 40, {"no_cull": 16}),
+        ("scaled 6000 stream block kernel", rt.scaled_scene(6000, max_depth=0), 48, 28, {"no_cull": 16}),
         ("scaled 200 strict", rt.scaled_scene(200, max_depth=0), 48, 24, {"strict": True}),
         ("scaled 6000 stream", rt.scaled_scene(6000, max_depth=1), 48, 28, {}),
         ("scaled 6000 stream nocull", rt.scaled_scene(6000, max_depth=0), 48, 28, {"no_cull": 1}),
