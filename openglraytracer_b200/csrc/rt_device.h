@@ -31,7 +31,8 @@
 /* from this many hot objects the large-scene kernels put the packet (cone) tests in front of the per-ray loops */
 #define RT_PACKET_MIN_OBJECTS 96
 /* from this many hot objects the CTA-level packet tests (rt_kernel_block.cuh) pay for their barriers */
-#define RT_BLOCK_MIN_OBJECTS 32768
+#define RT_BLOCK_MIN_OBJECTS 16384
+#define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
 
 /* Cold record: 64 words. */
 struct RtCold {
@@ -104,6 +105,8 @@ struct RtParams {
     int32_t cull;               /* 1: large-scene kernels run the slab test behind the bounding-sphere test */
     int32_t packet;             /* 1: coherent packets (primary rays, shadow rays per light) run the cone test first */
     int32_t block;              /* 1: CTA-level packet tests (blocks of 2 x 4 work items share the pass over the scene) */
+    uint32_t* blist;            /* block kernel: per-CTA shadow-candidate lists, blist_stride entries each */
+    int32_t blist_stride;
     const float* extent;        /* scene extent E (max |centre| + radius over objects and lights), written by the prologue */
 };
 

@@ -129,6 +129,7 @@ struct rt_context {
     DevBuf<rt_object> d_objs;                 // device prologue inputs
     DevBuf<int32_t> d_kind, d_hot;
     DevBuf<unsigned int> d_extent;
+    DevBuf<uint32_t> d_blist;                 // block kernel: shadow-candidate lists, one slice per resident CTA
     int prologue_mode = RT_PROLOGUE_AUTO;
     bool strict_ready = false;                // d_box_strict holds the current scene
     std::vector<rt_object> objs_copy;
@@ -293,7 +294,7 @@ int rt_destroy(rt_context* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_obj_lrec.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
-    c->d_objs.release(); c->d_kind.release(); c->d_hot.release(); c->d_extent.release();
+    c->d_objs.release(); c->d_kind.release(); c->d_hot.release(); c->d_extent.release(); c->d_blist.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -505,6 +506,12 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.packet = (P.cull && !(o.no_cull & 4) && c->n_box + c->n_sph >= RT_PACKET_MIN_OBJECTS) ? 1 : 0;
     P.block = (P.packet && !(o.no_cull & 8) && (c->n_box + c->n_sph >= RT_BLOCK_MIN_OBJECTS || (o.no_cull & 16))) ? 1 : 0;
     P.extent = reinterpret_cast<const float*>(c->d_extent.p);
+    if (P.block) {
+        // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
+        P.blist_stride = c->n_box + c->n_sph;
+        CU(c->d_blist.reserve((size_t)RT_MAX_CTAS_PER_SM * c->sm_count * (size_t)P.blist_stride));
+        P.blist = c->d_blist.p;
+    }
     P.n_lit = (P.cull && !P.packet && !(o.no_cull & 2)) ? c->n_lit : 0;
     P.n_lit_batch = c->n_lit_total <= 3 ? c->n_lit_total : -1;
     memcpy(P.lit, c->lit, sizeof(P.lit)); memcpy(P.amb_sum, c->amb_sum, sizeof(P.amb_sum));

@@ -22,12 +22,11 @@
 
 constexpr int kBlkW = 2, kBlkH = 4;              // work items per block
 constexpr int kListCap = 2048;                   // primary candidates per block; an overflowing block falls back to packet_trace
-constexpr int kListCapB = 2048;                  // shadow candidates per block (up to three lights)
-constexpr float kBlockMinCos = kConeMinCos;      // wider block cones: the block falls back to packet_trace
+constexpr float kBlockMinCos = 0.1f;             // light cones of a block may be wide: they only feed the list, which cannot
+                                                 // overflow (list B lives in HBM / L2, one slice of n_hot entries per CTA)
 
 struct BlockShared {
     uint32_t list_a[kListCap];                   // primary candidates of the block: hot index | 1 << 28
-    uint32_t list_b[kListCapB];                  // shadow candidates: hot index | lit-light mask << 28
     float sum[kWarps][12];                       // per warp, per light slot: sum of unit directions (xyz), count
     float mx[kWarps][12];                        // per warp, per light slot: max sin^2, max |L - p|^2, in-cone flag
     unsigned count_a, count_b[2];                // count_b: one per sample parity (reset while the other is in use)
@@ -81,7 +80,7 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
 
 // One warp: its 3 rays per lane against the entries of a block list whose mask has bit `kbit`; the
 // warp's own cone first (one entry per lane), then candidate_test for the survivors.
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool COUNT, bool GLOB>
 __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, const uint32_t* __restrict__ list, int count, unsigned kbit,
                                         const Cone* __restrict__ cone_in, bool use_cone, float grow, float live_min, float pad1, float pad2,
                                         bool shared, const V3* __restrict__ o_in, const V3* __restrict__ d_in,
@@ -93,7 +92,8 @@ __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, con
     for (int e0 = 0; e0 < count; e0 += 32) {
         if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
         const int e = e0 + lane;
-        const uint32_t ent = e < count ? list[e] : 0u;
+        // GLOB: the list was written to global memory by this CTA during this launch: coherent (L2) loads
+        const uint32_t ent = e < count ? (GLOB ? __ldcg(list + e) : list[e]) : 0u;
         const int hot = (int)(ent & 0x0fffffffu);
         const bool sel = e < count && ((ent >> 28) & kbit) != 0u;
         const bool sph = hot >= P.n_box;
@@ -160,6 +160,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
         }
     }
     BlockShared* bs = reinterpret_cast<BlockShared*>(smem_f4 + off4);
+    uint32_t* __restrict__ list_b = P.blist + (size_t)blockIdx.x * P.blist_stride;    // shadow candidates: hot index | lit-light mask << 28
     if (threadIdx.x == 0) { bs->count_a = 0u; bs->count_b[0] = 0u; bs->count_b[1] = 0u; }
     __syncthreads();
 
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
             const V3 cd = primary_dir(P, cam, x0 + (lane & 1) * kBlkW * 8 * NP, yb + ((lane >> 1) & 1) * kBlkH * 4, 0.0f, 0.0f);
             const V3 x = cross3(bc[0].axis, cd);
             const float s2 = fminf(__fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z))), 1.0f);
-            a_ok = __all_sync(kFull, dot3(bc[0].axis, cd) >= kBlockMinCos);       // same inputs in every warp: CTA-uniform
+            a_ok = __all_sync(kFull, dot3(bc[0].axis, cd) >= kConeMinCos);       // same inputs in every warp: CTA-uniform
             cone_close(bc[0], warp_max_nonneg(s2), kFar * 1.001f);
         }
         if (a_ok) block_filter<SMEM, COUNT, 1>(P, w, bc, 1u, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
@@ -247,7 +248,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 cone_close(pc[0], warp_max_nonneg(s2), kFar * 1.001f);
             }
             if (packet && use_a) {
-                list_trace<SMEM, COUNT>(P, w, bs->list_a, na, 1u, pc, true, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
+                list_trace<SMEM, COUNT, false>(P, w, bs->list_a, na, 1u, pc, true, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
             } else if (packet) {
                 packet_trace<SMEM, COUNT, 1>(P, w, pc, 1u, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
             } else {
@@ -364,11 +365,11 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 }
                 // every thread holds the same `on`, `b_ok`, cones (all read from shared memory): CTA-uniform
                 if (b_ok && on != 0u)
-                    block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, 0.0101f, pk_pad1, pk_pad2, bs->list_b, kListCapB, &bs->count_b[s & 1], cnt);
+                    block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
                 __syncthreads();                                                    // list B complete
                 const int nb = (int)bs->count_b[s & 1];
                 if (threadIdx.x == 0) bs->count_b[(s + 1) & 1] = 0u;                // its readers (sample s - 1) are past two barriers
-                const bool use_b = b_ok && nb <= kListCapB;
+                const bool use_b = b_ok && nb <= P.blist_stride;
 
                 // ---- this warp's root shadow rays, light by light (one cone over its own 96 hit points)
                 if (packet) {
@@ -413,7 +414,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             if (!narrow && !use_b) { have_sb = false; break; }                    // wide packet, no list: per tile in trace_sample
                             cone_close(wc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
                             int unused[kShadowBatch] = {-1, -1, -1};
-                            if (use_b) list_trace<SMEM, COUNT>(P, w, bs->list_b, nb, 1u << k, wc, narrow, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
+                            if (use_b) list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, narrow, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
                             else packet_trace<SMEM, COUNT, 1>(P, w, wc, 1u, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
