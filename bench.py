@@ -57,7 +57,8 @@ WORKLOADS = {
 BATCH_FRAMES = 256
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel, from the committed
 # `ncu --set full` captures (profiles/r1_ncu_full_*.txt); the 8.3 MB frame mostly stays in the 126 MB L2.
-NCU_DRAM_BYTES = {"builtin_1080p_d4": 62720 + 683520, "scaled_1k_1080p_d0": 1194752 + 2989568}
+NCU_DRAM_BYTES = {"builtin_1080p_d4": 58624 + 1224192, "scaled_1k_1080p_d0": 10005760 + 132145152,
+                  "scaled_64k_1080p_d0": 12879104 + 117420544}
 DEFAULT_WORKLOAD = "builtin_1080p_d4"
 METRIC = "Mrays/s (rays x bounces)"
 UNIT = "Mrays/s"
@@ -71,13 +72,16 @@ F_BOX, F_SPH, F_HIT, F_LIGHT, F_PRIMARY = 59.0, 41.0, 45.0, 95.0, 76.0
 # + d.oc 5 + discriminant 3 + compare 1, counted as 12 per ray; a sphere test that goes on to its roots
 # then costs the remaining 41 - 17 = 24.
 F_CULL, F_SPH_ROOTS = 12.0, 24.0
+# Packet (cone) test of one object against one cone, one object per lane:
+# v = c - apex 3, h = v.axis 5, v x axis 9, p^2 5, rhs 2, far 1, three products 3, h^2 + p^2 2, compares 3.
+F_PACKET = 33.0
 
 
 def algorithmic_flops(st, samples):
     """Flops of the tests actually EXECUTED (skipped tests are never credited)."""
     f_sph = F_SPH_ROOTS if st["cull_tests"] else F_SPH
     return (F_BOX * st["box_tests"] + f_sph * st["sphere_tests"] + F_CULL * st["cull_tests"] +
-            F_HIT * st["hit_nodes"] + F_LIGHT * st["shadow_rays"] + F_PRIMARY * samples)
+            F_PACKET * st.get("packet_tests", 0) + F_HIT * st["hit_nodes"] + F_LIGHT * st["shadow_rays"] + F_PRIMARY * samples)
 
 
 def make_scene(mod, kind, n, depth):
@@ -395,16 +399,19 @@ def run_gpu(args, wl_name, wl):
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved / peak_tf, "traffic": NCU_DRAM_BYTES.get(wl_name),
                          "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/); algorithmic bytes = the "
-                                         "%d-byte frame + a few KB of scene: FP32-issue bound, not HBM" % (nfr * w * h * 4),
+                                         "%d-byte frame + the scene records: FP32-issue bound, not HBM; the large-scene "
+                                         "kernels also write back their per-thread pending-ray stacks (1.4 KB x 75 776 "
+                                         "threads)" % (nfr * w * h * 4),
                          "peak_source": "FP32 FMA-chain microbenchmark in this run (MEASURED_PEAKS.json has no FP32 "
                                         "figure); nominal 148 SM x 128 x 2 x 1.965 GHz = 74.4",
                          "algorithmic_flops_per_launch": flops_per_frame, "kernel_ms": kernel_ms,
                          "box_tests": int(st["box_tests"]), "sphere_tests": int(st["sphere_tests"]),
                          "bounding_sphere_tests": int(st["cull_tests"]),
+                         "packet_cone_tests": int(st.get("packet_tests", 0)),
                          "lane_use": st["nodes"] / max(1, 32 * st["warp_iters"]),
                          "flops_per_unit": "slab test 59, sphere 41 (24 after its discriminant), bounding-sphere / "
-                                           "discriminant test 12, hit resolve 45, shaded light 95, primary ray 76; "
-                                           "executed tests only"},
+                                           "discriminant test 12, packet cone test 33 per (object, cone), hit resolve 45, "
+                                           "shaded light 95, primary ray 76; executed tests only"},
             "clocks": clocks,
         }
         if bands:

@@ -203,8 +203,10 @@ def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
     blk, st_blk = tracer.render(sc, cam, w, h, want_stats=True, no_cull=16)
     assert np.array_equal(on, blk)
     assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=16))
+    warp_img, st_warp = tracer.render(sc, cam, w, h, want_stats=True, no_cull=8)
+    assert np.array_equal(on, warp_img)
     assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=8))
-    assert st_blk["rays"] == st_on["rays"] and 0 < st_blk["packet_tests"] < st_on["packet_tests"]
+    assert st_blk["rays"] == st_warp["rays"] and 0 < st_blk["packet_tests"] < st_warp["packet_tests"]
     _, st_ray = tracer.render(sc, cam, w, h, want_stats=True, no_cull=4)
     assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
     assert st_off["cull_tests"] == 0 and st_on["cull_tests"] > 0
