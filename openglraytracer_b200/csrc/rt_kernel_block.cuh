@@ -35,10 +35,18 @@ struct BlockShared {
 };
 constexpr int kBlockSharedBytes = (int)((sizeof(BlockShared) + 15) / 16 * 16);
 
+// Rays that start within `radius` of the apex and run toward it stay inside that ball: the bounding sphere
+// (c, rp) can only matter if it reaches into the ball.
+__device__ __forceinline__ bool ball_pass(V3 apex, float radius, float4 c, float rp) {
+    const V3 v = mk(c.x - apex.x, c.y - apex.y, c.z - apex.z);
+    const float far = radius + rp;
+    return __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z))) <= __fmul_rn(far, far);
+}
+
 // All threads of the CTA: one object per thread and trip against NC cones; hits are appended to `list`.
 template <bool SMEM, bool COUNT, int NC>
 __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w, const Cone (&cone)[NC], unsigned on,
-                                             float grow, float pad1, float pad2, uint32_t* __restrict__ list, int cap,
+                                             const float (&ball)[NC], float grow, float pad1, float pad2, uint32_t* __restrict__ list, int cap,
                                              unsigned* __restrict__ counter, RtCounters& cnt) {
     const int n_hot = P.n_box + P.n_sph;
     const unsigned lt_mask = (1u << w.lane) - 1u;
@@ -62,8 +70,10 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
             const float rp = packet_radius(c[b].w, sph, grow, pad1, pad2);
             unsigned cm = 0u;
 #pragma unroll
-            for (int k = 0; k < NC; ++k)
+            for (int k = 0; k < NC; ++k) {
                 if (NC == 1 || ((on >> k) & 1u)) cm |= cone_pass(cone[k], c[b], rp) ? (1u << k) : 0u;
+                if (ball[k] > 0.0f) cm |= ball_pass(cone[k].apex, ball[k], c[b], rp) ? (1u << k) : 0u;     // CTA-uniform branch
+            }
             if (!in) cm = 0u;
             if (COUNT && in) cnt.packet_tests += (unsigned long long)(NC == 1 ? 1 : __popc(on));
             const unsigned mask = __ballot_sync(kFull, cm != 0u);
@@ -82,7 +92,7 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
 // warp's own cone first (one entry per lane), then candidate_test for the survivors.
 template <bool SMEM, bool COUNT, bool GLOB>
 __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, const uint32_t* __restrict__ list, int count, unsigned kbit,
-                                        const Cone* __restrict__ cone_in, bool use_cone, float grow, float live_min, float pad1, float pad2,
+                                        const Cone* __restrict__ cone_in, int mode, float ball_r, float grow, float live_min, float pad1, float pad2,
                                         bool shared, const V3* __restrict__ o_in, const V3* __restrict__ d_in,
                                         float* __restrict__ best_io, int* __restrict__ bidx_io, RtCounters& cnt) {
     RaySet rs;
@@ -101,7 +111,10 @@ __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, con
         if (SMEM) c = smem_f4[sph ? w.sph_off4 + (uint32_t)(hot - P.n_box) : w.box_off4 + (uint32_t)hot];
         else c = sph ? __ldg(P.sph_hot + (hot - P.n_box)) : __ldg(P.box_cull + hot);
         const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
-        const bool pass = sel && (!use_cone || cone_pass(cone, c, rp));     // a wide warp cone: every selected entry goes on
+        // mode 0: every selected entry goes on (wide warp cone); 1: the warp's cone; 2: no cone (only near points);
+        // ball_r > 0: plus the ball around the apex that holds the warp's near points
+        const bool pass = sel && (mode == 0 || (mode == 1 && cone_pass(cone, c, rp)) ||
+                                  (ball_r > 0.0f && ball_pass(cone.apex, ball_r, c, rp)));
         if (COUNT) cnt.packet_tests += sel;
         unsigned mask = __ballot_sync(kFull, pass);
         while (mask) {
@@ -207,7 +220,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
             a_ok = __all_sync(kFull, dot3(bc[0].axis, cd) >= kConeMinCos);       // same inputs in every warp: CTA-uniform
             cone_close(bc[0], warp_max_nonneg(s2), kFar * 1.001f);
         }
-        if (a_ok) block_filter<SMEM, COUNT, 1>(P, w, bc, 1u, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
+        const float no_ball[1] = {0.0f};
+        if (a_ok) block_filter<SMEM, COUNT, 1>(P, w, bc, 1u, no_ball, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
         __syncthreads();                                                        // list A complete
         const int na = (int)bs->count_a;
         const bool use_a = a_ok && na <= kListCap;
@@ -248,7 +262,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 cone_close(pc[0], warp_max_nonneg(s2), kFar * 1.001f);
             }
             if (packet && use_a) {
-                list_trace<SMEM, COUNT, false>(P, w, bs->list_a, na, 1u, pc, true, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
+                list_trace<SMEM, COUNT, false>(P, w, bs->list_a, na, 1u, pc, 1, 0.0f, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
             } else if (packet) {
                 packet_trace<SMEM, COUNT, 1>(P, w, pc, 1u, 0.0f, 1e-45f, pk_pad1, pk_pad2, true, o3, dir, best, bidx, cnt);
             } else {
@@ -299,17 +313,34 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     const RtLightDev* __restrict__ L = P.lights + P.lit[k < n_lights_b ? k : 0];
                     lp[k] = mk(L->position[0], L->position[1], L->position[2]);
                 }
+                // Hit points much closer to the light than the rest (an object next to a lamp, seen in front of a far
+                // wall) would blow the cone up; they go into a ball around the light instead: a shadow ray that
+                // starts within r of L and runs toward L stays within r of L.  near = closer than a quarter of the
+                // warp's mean distance; each warp may classify as it likes, every point lands in the cone or the ball.
                 V3 u[kShadowBatch][kShadowBatch];        // [light][tile]
                 float l2[kShadowBatch][kShadowBatch];
+                bool nearp[kShadowBatch][kShadowBatch];
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
-                    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                    float dsum = 0.0f, dn = 0.0f;
 #pragma unroll
                     for (int q = 0; q < kShadowBatch; ++q) {
                         const V3 v = hp[q] - lp[k];
                         l2[k][q] = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
                         u[k][q] = v * rsqrtf(l2[k][q]);
-                        if (sh[q] && k < n_lights_b) { acc[0] += u[k][q].x; acc[1] += u[k][q].y; acc[2] += u[k][q].z; acc[3] += 1.0f; }
+                        if (sh[q]) { dsum += sqrt_approx(l2[k][q]); dn += 1.0f; }
+                    }
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) {
+                        dsum += __shfl_xor_sync(kFull, dsum, off);
+                        dn += __shfl_xor_sync(kFull, dn, off);
+                    }
+                    const float thr = dn > 0.0f ? 0.25f * dsum / dn : 0.0f;
+                    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                    for (int q = 0; q < kShadowBatch; ++q) {
+                        nearp[k][q] = sh[q] && l2[k][q] < thr * thr;
+                        if (sh[q] && !nearp[k][q] && k < n_lights_b) { acc[0] += u[k][q].x; acc[1] += u[k][q].y; acc[2] += u[k][q].z; acc[3] += 1.0f; }
                     }
 #pragma unroll
                     for (int off = 16; off > 0; off >>= 1) {
@@ -334,38 +365,44 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     lc[k].apex = lp[k];
                     lc[k].axis = normalize3(mk(t4[0], t4[1], t4[2]));
                     if (k < n_lights_b && t4[3] > 0.0f) on |= 1u << k;
-                    // ... then the half-angle, the reach and "all inside kConeMinCos" over the CTA
-                    float s2 = 0.0f, lmax = 0.0f;
+                    // ... then the half-angle, the reach and "all inside kBlockMinCos" over the CTA (far points), and the
+                    // radius of the ball (near points)
+                    float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f;
                     bool in_cone = true;
 #pragma unroll
                     for (int q = 0; q < kShadowBatch; ++q) {
                         const V3 x = cross3(lc[k].axis, u[k][q]);
                         const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
-                        if (sh[q]) {
+                        if (sh[q] && !nearp[k][q]) {
                             s2 = fmaxf(s2, fminf(s2q, 1.0f));
                             lmax = fmaxf(lmax, l2[k][q]);
                             in_cone = in_cone && dot3(lc[k].axis, u[k][q]) >= kBlockMinCos;    // NaN -> false
                         }
+                        if (nearp[k][q] && k < n_lights_b) nmax = fmaxf(nmax, l2[k][q]);
                     }
-                    const float s2w = warp_max_nonneg(s2), lw = warp_max_nonneg(lmax);
+                    const float s2w = warp_max_nonneg(s2), lw = warp_max_nonneg(lmax), nw = warp_max_nonneg(nmax);
                     const bool okw = __all_sync(kFull, in_cone);
-                    if (lane == 0) { bs->mx[warp][4 * k] = s2w; bs->mx[warp][4 * k + 1] = lw; bs->mx[warp][4 * k + 2] = okw ? 1.0f : 0.0f; }
+                    if (lane == 0) { bs->mx[warp][4 * k] = s2w; bs->mx[warp][4 * k + 1] = lw; bs->mx[warp][4 * k + 2] = okw ? 1.0f : 0.0f; bs->mx[warp][4 * k + 3] = nw; }
                 }
                 __syncthreads();                                                    // maxima visible
                 bool b_ok = true;
+                float ball[kShadowBatch];
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
-                    float s2 = 0.0f, lmax = 0.0f;
+                    float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f;
                     for (int ww = 0; ww < kWarps; ++ww) {
                         s2 = fmaxf(s2, bs->mx[ww][4 * k]);
                         lmax = fmaxf(lmax, bs->mx[ww][4 * k + 1]);
+                        nmax = fmaxf(nmax, bs->mx[ww][4 * k + 3]);
                         if ((on >> k) & 1u) b_ok = b_ok && bs->mx[ww][4 * k + 2] != 0.0f;
                     }
                     cone_close(lc[k], s2, __fmaf_rn(sqrt_approx(lmax), 1.0001f, 0.0101f));
+                    ball[k] = nmax > 0.0f ? __fmaf_rn(sqrt_approx(nmax), 1.0001f, 0.0101f) : 0.0f;
                 }
+                const bool any_b = on != 0u || ball[0] > 0.0f || ball[1] > 0.0f || ball[2] > 0.0f;
                 // every thread holds the same `on`, `b_ok`, cones (all read from shared memory): CTA-uniform
-                if (b_ok && on != 0u)
-                    block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
+                if (b_ok && any_b)
+                    block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
                 __syncthreads();                                                    // list B complete
                 const int nb = (int)bs->count_b[s & 1];
                 if (threadIdx.x == 0) bs->count_b[(s + 1) & 1] = 0u;                // its readers (sample s - 1) are past two barriers
@@ -380,6 +417,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             const V3 lpk = k == 0 ? lp[0] : (k == 1 ? lp[1] : lp[2]);
                             V3 sd3[kShadowBatch], uu[kShadowBatch];
                             float ll[kShadowBatch], sbk[kShadowBatch];
+                            bool nq[kShadowBatch];
                             V3 sm = mk(0.0f, 0.0f, 0.0f);
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
@@ -387,7 +425,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                                 sbk[q] = sh[q] ? 1.0f : 0.0f;
                                 ll[q] = __fmaf_rn(sd3[q].x, sd3[q].x, __fmaf_rn(sd3[q].y, sd3[q].y, __fmul_rn(sd3[q].z, sd3[q].z)));
                                 uu[q] = sd3[q] * -rsqrtf(ll[q]);
-                                if (sh[q]) sm = sm + uu[q];
+                                nq[q] = k == 0 ? nearp[0][q] : (k == 1 ? nearp[1][q] : nearp[2][q]);
+                                if (sh[q] && !nq[q]) sm = sm + uu[q];
                             }
 #pragma unroll
                             for (int off = 16; off > 0; off >>= 1) {
@@ -398,23 +437,29 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             Cone wc[1];
                             wc[0].apex = lpk;
                             wc[0].axis = normalize3(sm);
-                            float s2 = 0.0f, lmax = 0.0f;
-                            bool in_cone = true;
+                            float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f;
+                            bool in_cone = true, far_pt = false;
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
                                 const V3 x = cross3(wc[0].axis, uu[q]);
                                 const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
-                                if (sh[q]) {
+                                if (sh[q] && !nq[q]) {
+                                    far_pt = true;
                                     s2 = fmaxf(s2, fminf(s2q, 1.0f));
                                     lmax = fmaxf(lmax, ll[q]);
                                     in_cone = in_cone && dot3(wc[0].axis, uu[q]) >= kConeMinCos;
                                 }
+                                if (nq[q]) nmax = fmaxf(nmax, ll[q]);
                             }
                             const bool narrow = __all_sync(kFull, in_cone);
-                            if (!narrow && !use_b) { have_sb = false; break; }                    // wide packet, no list: per tile in trace_sample
+                            const bool has_far = __any_sync(kFull, far_pt);
+                            const float nw = warp_max_nonneg(nmax);
+                            const float ball_r = nw > 0.0f ? __fmaf_rn(sqrt_approx(nw), 1.0001f, 0.0101f) : 0.0f;
+                            // without the block list the per-warp scan needs one narrow cone and nothing else
+                            if (!use_b && (!narrow || ball_r > 0.0f)) { have_sb = false; break; }
                             cone_close(wc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
                             int unused[kShadowBatch] = {-1, -1, -1};
-                            if (use_b) list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, narrow, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
+                            if (use_b) list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, !has_far ? 2 : (narrow ? 1 : 0), ball_r, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
                             else packet_trace<SMEM, COUNT, 1>(P, w, wc, 1u, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
