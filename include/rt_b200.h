@@ -137,7 +137,8 @@ typedef struct rt_options {
                                * test first); bit 1 = shadow rays do not use the per-light records; bit 2 = no packet
                                * (cone) tests, every ray meets every bounding sphere itself; bit 3 = no CTA-level packet
                                * tests (each warp scans the scene for its own packets); bit 4 = CTA-level packet tests
-                               * also below RT_BLOCK_MIN_OBJECTS objects (test switch) */
+                               * also below RT_BLOCK_MIN_OBJECTS objects (test switch); bit 5 = shadow packets without
+                               * their fan planes (cone and reach only) */
 } rt_options;
 
 #define RT_HOST_STORE_AUTO   0

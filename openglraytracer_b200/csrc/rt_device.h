@@ -108,6 +108,8 @@ struct RtParams {
     uint32_t* blist;            /* block kernel: per-CTA shadow-candidate lists, blist_stride entries each */
     int32_t blist_stride;
     const float* extent;        /* scene extent E (max |centre| + radius over objects and lights), written by the prologue */
+    int32_t fan;                /* 1: shadow packets of the block kernel also carry a fan plane (rt_kernel.cuh: Cone::nrm) */
+    uint32_t* blk_log;          /* block kernel, instrumented twin only (RT_BLOCK_LOG=path): 16 words per block, see tools/block_log.py */
 };
 
 #endif

@@ -130,6 +130,7 @@ struct rt_context {
     DevBuf<int32_t> d_kind, d_hot;
     DevBuf<unsigned int> d_extent;
     DevBuf<uint32_t> d_blist;                 // block kernel: shadow-candidate lists, one slice per resident CTA
+    DevBuf<uint32_t> d_blklog;                // block kernel, RT_BLOCK_LOG=path: per-block timing records of the instrumented twin
     int prologue_mode = RT_PROLOGUE_AUTO;
     bool strict_ready = false;                // d_box_strict holds the current scene
     std::vector<rt_object> objs_copy;
@@ -294,7 +295,7 @@ int rt_destroy(rt_context* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_obj_lrec.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
-    c->d_objs.release(); c->d_kind.release(); c->d_hot.release(); c->d_extent.release(); c->d_blist.release();
+    c->d_objs.release(); c->d_kind.release(); c->d_hot.release(); c->d_extent.release(); c->d_blist.release(); c->d_blklog.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -505,6 +506,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     // fallback for incoherent packets and are left out (they would halve the resident capacity).
     P.packet = (P.cull && !(o.no_cull & 4) && c->n_box + c->n_sph >= RT_PACKET_MIN_OBJECTS) ? 1 : 0;
     P.block = (P.packet && !(o.no_cull & 8) && (c->n_box + c->n_sph >= RT_BLOCK_MIN_OBJECTS || (o.no_cull & 16))) ? 1 : 0;
+    P.fan = (P.block && !(o.no_cull & 32)) ? 1 : 0;
     P.extent = reinterpret_cast<const float*>(c->d_extent.p);
     if (P.block) {
         // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
@@ -551,6 +553,15 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
 
     const bool count = o.stats != nullptr;
     if (count) CU(cudaMemsetAsync(c->d_cnt.p, 0, sizeof(RtCounters), st));
+    // profiling aid: RT_BLOCK_LOG=path makes the instrumented twin of the block kernel write one 64-byte
+    // record per block (start, duration, list sizes, per-warp times), dumped to `path` after the render
+    const char* blk_log_path = (count && P.block) ? getenv("RT_BLOCK_LOG") : nullptr;
+    size_t blk_log_words = 0;
+    if (blk_log_path && *blk_log_path) {
+        blk_log_words = (size_t)((P.tiles_x + 5) / 6) * ((P.tiles_y + 3) / 4) * n_frames * 16;
+        CU(c->d_blklog.reserve(blk_log_words));
+        CU(cudaMemsetAsync(c->d_blklog.p, 0, blk_log_words * 4, st));
+    }
     CU(cudaMemsetAsync(c->d_tile.p, 0, 2 * sizeof(unsigned long long), st));
     if (o.stats) CU(cudaEventRecord(c->ev[0], st));
     CU(o.strict ? rt_strict::launch(P, grid, false, st) : rt_fast::launch(P, grid, false, st));
@@ -559,7 +570,9 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     if (count) {
         // instrumented twin: same kernel with counters, run after the timed one (results identical)
         CU(cudaMemsetAsync(c->d_tile.p, 0, 2 * sizeof(unsigned long long), st));
+        if (blk_log_words) P.blk_log = c->d_blklog.p;
         CU(o.strict ? rt_strict::launch(P, grid, true, st) : rt_fast::launch(P, grid, true, st));
+        P.blk_log = nullptr;
         g_launches++;
     }
 
@@ -587,6 +600,11 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         s->cull_tests = hc.cull_tests; s->warp_iters = hc.warp_iters; s->packet_tests = hc.packet_tests;
         CU(cudaEventElapsedTime(&s->kernel_ms, c->ev[0], c->ev[1]));
         CU(cudaEventElapsedTime(&s->total_ms, c->ev[2], c->ev[3]));
+        if (blk_log_words) {
+            std::vector<uint32_t> hl(blk_log_words);
+            CU(cudaMemcpy(hl.data(), c->d_blklog.p, blk_log_words * 4, cudaMemcpyDeviceToHost));
+            if (FILE* f = fopen(blk_log_path, "wb")) { fwrite(hl.data(), 4, blk_log_words, f); fclose(f); }
+        }
     }
     return RT_OK;
 }

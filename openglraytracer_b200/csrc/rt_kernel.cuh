@@ -799,9 +799,14 @@ __device__ __forceinline__ void lights_tile(const RtParams& P, const float4* __r
 // above, so a frame is byte-identical with the packet tests on or off (tests/test_gpu_parity.py).
 // -------------------------------------------------------------------------
 struct Cone {
-    V3 apex, axis;
+    V3 apex, axis;    // axis = 0: no angular bound (everything within `reach` of the apex passes the cone part)
     float s, c2;      // padded sin(theta), 1 - s^2
     float reach;      // no ray of the packet extends further than this from the apex
+    // Fan: the packet's rays also stay within `hw` of the plane through the apex with unit normal `nrm`.  Shadow
+    // rays of hit points strung out along a thin view frustum subtend a wide angle at the light but lie
+    // close to the plane through the light and the frustum's axis.  hw = 3e38: no plane.
+    V3 nrm;
+    float hw;
 };
 
 __device__ __forceinline__ V3 cross3(V3 a, V3 b) {
@@ -812,6 +817,7 @@ __device__ __forceinline__ float warp_max_nonneg(float v) {      // v >= 0: floa
     return __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(v)));
 }
 // c = (centre, .), rp = padded bounding radius (NaN for a box that can never be hit -> false)
+template <bool SLAB = false>
 __device__ __forceinline__ bool cone_pass(const Cone& k, float4 c, float rp) {
     const V3 v = mk(c.x - k.apex.x, c.y - k.apex.y, c.z - k.apex.z);
     const float h = __fmaf_rn(v.x, k.axis.x, __fmaf_rn(v.y, k.axis.y, __fmul_rn(v.z, k.axis.z)));
@@ -819,13 +825,34 @@ __device__ __forceinline__ bool cone_pass(const Cone& k, float4 c, float rp) {
     const float p2 = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
     const float rhs = __fmaf_rn(h, k.s, rp);
     const float far = k.reach + rp;
-    return rhs >= 0.0f && __fmul_rn(p2, k.c2) <= __fmul_rn(rhs, rhs) && __fmaf_rn(h, h, p2) <= __fmul_rn(far, far);
+    const float v2 = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
+    bool pass = rhs >= 0.0f && __fmul_rn(p2, k.c2) <= __fmul_rn(rhs, rhs) && v2 <= __fmul_rn(far, far);
+    if (SLAB) {
+        const float sl = fabsf(__fmaf_rn(v.x, k.nrm.x, __fmaf_rn(v.y, k.nrm.y, __fmul_rn(v.z, k.nrm.z))));
+        pass = pass && sl <= k.hw + rp;
+    }
+    return pass;
 }
 // Finishes a cone from the warp's maxima: s2 = max |axis x u|^2 over the packet's unit directions u.
 __device__ __forceinline__ void cone_close(Cone& k, float s2max, float reach) {
     k.s = __fmaf_rn(sqrt_approx(s2max), 1.0005f, 4e-6f);
     k.c2 = fmaxf(1.0f - k.s * k.s, 0.0f);
     k.reach = reach;
+    k.nrm = mk(0.0f, 0.0f, 0.0f);
+    k.hw = 3e38f;
+}
+// Unit normal of the plane through a light and a view axis (a = the axis, b = eye - light); zero when the light
+// sits on the axis (then the cone is narrow anyway).
+__device__ __forceinline__ V3 fan_normal(V3 a, V3 b) {
+    const V3 x = cross3(a, b);
+    const float l2 = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+    return l2 > 1e-12f ? x * rsqrtf(l2) : mk(0.0f, 0.0f, 0.0f);
+}
+// hmax = max |nrm . (p - apex)| over the packet's hit points; pad1 = 2e-6 E covers the rounding of both dot products
+__device__ __forceinline__ void cone_fan(Cone& k, V3 nrm, float hmax, float pad1) {
+    const bool ok = (nrm.x != 0.0f || nrm.y != 0.0f || nrm.z != 0.0f) && hmax < 1e30f;      // NaN -> no plane
+    k.nrm = ok ? nrm : mk(0.0f, 0.0f, 0.0f);
+    k.hw = ok ? __fmaf_rn(hmax, 1.0005f, 4.0f * pad1) : 3e38f;
 }
 constexpr float kConeMinCos = 0.6f;     // wider packets take the per-ray loops
 // Padded bounding radius of a record.  Boxes: w = padded squared circumradius (prologue).  Spheres: w = r*r,

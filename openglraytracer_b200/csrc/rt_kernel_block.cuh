@@ -29,11 +29,23 @@ struct BlockShared {
     uint32_t list_a[kListCap];                   // primary candidates of the block: hot index | 1 << 28
     float sum[kWarps][12];                       // per warp, per light slot: sum of unit directions (xyz), count
     float mx[kWarps][12];                        // per warp, per light slot: max sin^2, max |L - p|^2, in-cone flag
+    float hw[kWarps][4];                         // per warp, per light slot: max distance of a hit point to the block's fan plane
     unsigned count_a, count_b[2];                // count_b: one per sample parity (reset while the other is in use)
     unsigned pad_;
     unsigned long long next;
 };
 constexpr int kBlockSharedBytes = (int)((sizeof(BlockShared) + 15) / 16 * 16);
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned smid() {
+    unsigned v;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(v));
+    return v;
+}
 
 // Rays that start within `radius` of the apex and run toward it stay inside that ball: the bounding sphere
 // (c, rp) can only matter if it reaches into the ball.
@@ -71,7 +83,7 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
             unsigned cm = 0u;
 #pragma unroll
             for (int k = 0; k < NC; ++k) {
-                if (NC == 1 || ((on >> k) & 1u)) cm |= cone_pass(cone[k], c[b], rp) ? (1u << k) : 0u;
+                if (NC == 1 || ((on >> k) & 1u)) cm |= cone_pass<NC != 1>(cone[k], c[b], rp) ? (1u << k) : 0u;
                 if (ball[k] > 0.0f) cm |= ball_pass(cone[k].apex, ball[k], c[b], rp) ? (1u << k) : 0u;     // CTA-uniform branch
             }
             if (!in) cm = 0u;
@@ -111,9 +123,9 @@ __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, con
         if (SMEM) c = smem_f4[sph ? w.sph_off4 + (uint32_t)(hot - P.n_box) : w.box_off4 + (uint32_t)hot];
         else c = sph ? __ldg(P.sph_hot + (hot - P.n_box)) : __ldg(P.box_cull + hot);
         const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
-        // mode 0: every selected entry goes on (wide warp cone); 1: the warp's cone; 2: no cone (only near points);
+        // mode 0: every selected entry goes on; 1: the warp's cone and fan plane; 2: no cone (only near points);
         // ball_r > 0: plus the ball around the apex that holds the warp's near points
-        const bool pass = sel && (mode == 0 || (mode == 1 && cone_pass(cone, c, rp)) ||
+        const bool pass = sel && (mode == 0 || (mode == 1 && cone_pass<true>(cone, c, rp)) ||
                                   (ball_r > 0.0f && ball_pass(cone.apex, ball_r, c, rp)));
         if (COUNT) cnt.packet_tests += sel;
         unsigned mask = __ballot_sync(kFull, pass);
@@ -191,6 +203,11 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
     cnt.cull_tests = cnt.warp_iters = 0ull;
 
     for (long long blk = blockIdx.x; blk < n_blocks;) {
+        // RT_BLOCK_LOG (instrumented twin only): when this block started, how long each warp worked, list sizes
+        const bool logging = COUNT && P.blk_log != nullptr;
+        unsigned long long log_t0 = 0ull;
+        unsigned log_nb = 0u, log_flags = 0u;
+        if (logging) log_t0 = global_ns();
         const int frame = (int)(blk / blocks_per_frame);
         const int bin = (int)(blk - (long long)frame * blocks_per_frame);
         const int by = bin / bx_n, bx = bin - by * bx_n;
@@ -225,6 +242,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
         __syncthreads();                                                        // list A complete
         const int na = (int)bs->count_a;
         const bool use_a = a_ok && na <= kListCap;
+        const unsigned long long log_ta = logging ? global_ns() : 0ull;
 
         V3 sum[NP];
 #pragma unroll
@@ -367,8 +385,9 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     if (k < n_lights_b && t4[3] > 0.0f) on |= 1u << k;
                     // ... then the half-angle, the reach and "all inside kBlockMinCos" over the CTA (far points), and the
                     // radius of the ball (near points)
-                    float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f;
+                    float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f, hmax = 0.0f;
                     bool in_cone = true;
+                    const V3 bn = fan_normal(bc[0].axis, org - lp[k]);      // the block's fan plane: through the light and the block's view axis
 #pragma unroll
                     for (int q = 0; q < kShadowBatch; ++q) {
                         const V3 x = cross3(lc[k].axis, u[k][q]);
@@ -377,26 +396,34 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             s2 = fmaxf(s2, fminf(s2q, 1.0f));
                             lmax = fmaxf(lmax, l2[k][q]);
                             in_cone = in_cone && dot3(lc[k].axis, u[k][q]) >= kBlockMinCos;    // NaN -> false
+                            hmax = fmaxf(hmax, fabsf(dot3(bn, hp[q] - lp[k])));
                         }
                         if (nearp[k][q] && k < n_lights_b) nmax = fmaxf(nmax, l2[k][q]);
                     }
                     const float s2w = warp_max_nonneg(s2), lw = warp_max_nonneg(lmax), nw = warp_max_nonneg(nmax);
+                    const float hwp = warp_max_nonneg(hmax < 1e30f ? hmax : 1e30f);                // NaN -> no plane
                     const bool okw = __all_sync(kFull, in_cone);
-                    if (lane == 0) { bs->mx[warp][4 * k] = s2w; bs->mx[warp][4 * k + 1] = lw; bs->mx[warp][4 * k + 2] = okw ? 1.0f : 0.0f; bs->mx[warp][4 * k + 3] = nw; }
+                    if (lane == 0) { bs->mx[warp][4 * k] = s2w; bs->mx[warp][4 * k + 1] = lw; bs->mx[warp][4 * k + 2] = okw ? 1.0f : 0.0f; bs->mx[warp][4 * k + 3] = nw; bs->hw[warp][k] = hwp; }
                 }
                 __syncthreads();                                                    // maxima visible
                 bool b_ok = true;
                 float ball[kShadowBatch];
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
-                    float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f;
+                    float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f, hmax = 0.0f;
+                    bool k_ok = true;
                     for (int ww = 0; ww < kWarps; ++ww) {
                         s2 = fmaxf(s2, bs->mx[ww][4 * k]);
                         lmax = fmaxf(lmax, bs->mx[ww][4 * k + 1]);
                         nmax = fmaxf(nmax, bs->mx[ww][4 * k + 3]);
-                        if ((on >> k) & 1u) b_ok = b_ok && bs->mx[ww][4 * k + 2] != 0.0f;
+                        hmax = fmaxf(hmax, bs->hw[ww][k]);
+                        k_ok = k_ok && bs->mx[ww][4 * k + 2] != 0.0f;
                     }
                     cone_close(lc[k], s2, __fmaf_rn(sqrt_approx(lmax), 1.0001f, 0.0101f));
+                    // hit points spread beyond kBlockMinCos as seen from the light: no angular bound, the reach and the
+                    // fan plane still hold
+                    if (!k_ok) lc[k].axis = mk(0.0f, 0.0f, 0.0f);
+                    cone_fan(lc[k], fan_normal(bc[0].axis, org - lp[k]), P.fan ? hmax : 3e38f, pk_pad1);
                     ball[k] = nmax > 0.0f ? __fmaf_rn(sqrt_approx(nmax), 1.0001f, 0.0101f) : 0.0f;
                 }
                 const bool any_b = on != 0u || ball[0] > 0.0f || ball[1] > 0.0f || ball[2] > 0.0f;
@@ -407,6 +434,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 const int nb = (int)bs->count_b[s & 1];
                 if (threadIdx.x == 0) bs->count_b[(s + 1) & 1] = 0u;                // its readers (sample s - 1) are past two barriers
                 const bool use_b = b_ok && nb <= P.blist_stride;
+                if (logging) { log_nb = (unsigned)nb; log_flags |= (use_b ? 1u : 2u) | (on << 4) | (ball[0] > 0.0f ? 0x100u : 0u) | (ball[1] > 0.0f ? 0x200u : 0u) | (ball[2] > 0.0f ? 0x400u : 0u); }
 
                 // ---- this warp's root shadow rays, light by light (one cone over its own 96 hit points)
                 if (packet) {
@@ -437,8 +465,9 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             Cone wc[1];
                             wc[0].apex = lpk;
                             wc[0].axis = normalize3(sm);
-                            float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f;
+                            float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f, hmax = 0.0f;
                             bool in_cone = true, far_pt = false;
+                            const V3 wn = fan_normal(pc[0].axis, org - lpk);     // the work item's fan plane
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
                                 const V3 x = cross3(wc[0].axis, uu[q]);
@@ -448,6 +477,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                                     s2 = fmaxf(s2, fminf(s2q, 1.0f));
                                     lmax = fmaxf(lmax, ll[q]);
                                     in_cone = in_cone && dot3(wc[0].axis, uu[q]) >= kConeMinCos;
+                                    hmax = fmaxf(hmax, fabsf(dot3(wn, sd3[q])));
                                 }
                                 if (nq[q]) nmax = fmaxf(nmax, ll[q]);
                             }
@@ -458,8 +488,13 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             // without the block list the per-warp scan needs one narrow cone and nothing else
                             if (!use_b && (!narrow || ball_r > 0.0f)) { have_sb = false; break; }
                             cone_close(wc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
+                            if (use_b) {
+                                if (!narrow) wc[0].axis = mk(0.0f, 0.0f, 0.0f);           // reach and fan plane only
+                                const float hwp = warp_max_nonneg(hmax < 1e30f ? hmax : 1e30f);
+                                cone_fan(wc[0], wn, P.fan ? hwp : 3e38f, pk_pad1);
+                            }
                             int unused[kShadowBatch] = {-1, -1, -1};
-                            if (use_b) list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, !has_far ? 2 : (narrow ? 1 : 0), ball_r, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
+                            if (use_b) list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, has_far ? 1 : 2, ball_r, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
                             else packet_trace<SMEM, COUNT, 1>(P, w, wc, 1u, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
@@ -502,6 +537,16 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     *reinterpret_cast<uint4*>(frame_out + pix * 4) = make_uint4(word, w1, w2, w3);
             } else if (valid[q]) {
                 *reinterpret_cast<uint32_t*>(frame_out + pix * 4) = word;
+            }
+        }
+        if (logging) {
+            uint32_t* rec = P.blk_log + blk * 16;
+            const unsigned long long t1 = global_ns();
+            if (lane == 0) rec[8 + warp] = (uint32_t)(t1 - log_t0);
+            if (threadIdx.x == 0) {
+                rec[0] = (uint32_t)log_t0; rec[1] = (uint32_t)(log_t0 >> 32);
+                rec[2] = (uint32_t)(log_ta - log_t0); rec[3] = (uint32_t)na; rec[4] = log_nb;
+                rec[5] = log_flags | (use_a ? 4u : 8u); rec[6] = smid(); rec[7] = blockIdx.x;
             }
         }
         // next block for the whole CTA; list A is reset for it (every warp is past its reads of both lists here
