@@ -114,6 +114,8 @@ typedef struct rt_stats {
     uint64_t cull_tests;      /* bounding-sphere / discriminant tests executed for live rays (large scenes) */
     uint64_t warp_iters;      /* bounce-loop iterations summed over warps; nodes/(32*warp_iters) = lane use */
     uint64_t packet_tests;    /* (object, cone) tests of the packet loops, one object per lane (large scenes) */
+    uint64_t group_passes;    /* bounce rays: passes over the scene made for a group of rays / hit points (per warp) */
+    uint64_t loop_passes;     /* bounce rays: passes made by the per-ray loops for what the groups left over (per warp) */
 } rt_stats;
 
 /* Extended options; zero-initialise then override (rt_options_default()). The
@@ -138,7 +140,8 @@ typedef struct rt_options {
                                * (cone) tests, every ray meets every bounding sphere itself; bit 3 = no CTA-level packet
                                * tests (each warp scans the scene for its own packets); bit 4 = CTA-level packet tests
                                * also below RT_BLOCK_MIN_OBJECTS objects (test switch); bit 5 = shadow packets without
-                               * their fan planes (cone and reach only) */
+                               * their fan planes (cone and reach only); bit 6 = bounce rays are not grouped into
+                               * packets (per-ray loops) */
 } rt_options;
 
 #define RT_HOST_STORE_AUTO   0

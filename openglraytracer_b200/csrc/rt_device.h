@@ -31,7 +31,7 @@
 /* from this many hot objects the large-scene kernels put the packet (cone) tests in front of the per-ray loops */
 #define RT_PACKET_MIN_OBJECTS 96
 /* from this many hot objects the CTA-level packet tests (rt_kernel_block.cuh) pay for their barriers */
-#define RT_BLOCK_MIN_OBJECTS 16384
+#define RT_BLOCK_MIN_OBJECTS 128
 #define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
 
 /* Cold record: 64 words. */
@@ -75,6 +75,8 @@ struct RtCounters {
     unsigned long long cull_tests;   /* bounding-sphere tests executed for live rays (large-scene kernels) */
     unsigned long long warp_iters;   /* bounce-loop iterations summed over warps: nodes / (32 * warp_iters) = lane utilisation */
     unsigned long long packet_tests; /* (object, cone) tests of the packet loops, one per lane (large-scene kernels) */
+    unsigned long long group_passes; /* per warp (lane 0): passes over the scene for a group of bounce rays / their hit points */
+    unsigned long long loop_passes;  /* per warp (lane 0): per-ray loop passes for bounce rays the groups left over */
 };
 
 struct RtParams {
@@ -109,6 +111,7 @@ struct RtParams {
     int32_t blist_stride;
     const float* extent;        /* scene extent E (max |centre| + radius over objects and lights), written by the prologue */
     int32_t fan;                /* 1: shadow packets of the block kernel also carry a fan plane (rt_kernel.cuh: Cone::nrm) */
+    float group_k;              /* > 0: secondary rays are traced as grouped packets; group radius^2 = E^2 * group_k, group_k = n_hot^(-2/3) */
     uint32_t* blk_log;          /* block kernel, instrumented twin only (RT_BLOCK_LOG=path): 16 words per block, see tools/block_log.py */
 };
 

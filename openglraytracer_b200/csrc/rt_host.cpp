@@ -507,6 +507,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.packet = (P.cull && !(o.no_cull & 4) && c->n_box + c->n_sph >= RT_PACKET_MIN_OBJECTS) ? 1 : 0;
     P.block = (P.packet && !(o.no_cull & 8) && (c->n_box + c->n_sph >= RT_BLOCK_MIN_OBJECTS || (o.no_cull & 16))) ? 1 : 0;
     P.fan = (P.block && !(o.no_cull & 32)) ? 1 : 0;
+    P.group_k = (P.packet && !(o.no_cull & 64)) ? (float)std::pow((double)(c->n_box + c->n_sph), -2.0 / 3.0) : 0.0f;
     P.extent = reinterpret_cast<const float*>(c->d_extent.p);
     if (P.block) {
         // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
@@ -598,6 +599,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         s->box_tests = hc.box_tests; s->sphere_tests = hc.sphere_tests; s->red_pixels = hc.red_pixels;
         s->rays_not_traversed = hc.pad;
         s->cull_tests = hc.cull_tests; s->warp_iters = hc.warp_iters; s->packet_tests = hc.packet_tests;
+        s->group_passes = hc.group_passes; s->loop_passes = hc.loop_passes;
         CU(cudaEventElapsedTime(&s->kernel_ms, c->ev[0], c->ev[1]));
         CU(cudaEventElapsedTime(&s->total_ms, c->ev[2], c->ev[3]));
         if (blk_log_words) {

@@ -71,8 +71,21 @@ __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y -
 __device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
 __device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ V3 operator*(float s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+// Everything that decides which object a ray hits or whether a shadow ray is blocked -- hit point, normal,
+// shadow / bounce ray origins and directions -- is written with madd() so that every instantiation of the
+// kernels (resident / streamed, with / without bounding tests, block kernel) rounds alike: left to the compiler,
+// FMA contraction is chosen per instantiation, and one ulp in a hit point flips hit decisions in scenes where the
+// shader's own quadratic is rounding noise (the +-3000 room of tests/test_gpu_parity.py).  Fast kernel: one
+// FMA.  Strict kernel (-fmad=false): multiply then add, the shader's operations.
+#if RT_STRICT
+__device__ __forceinline__ float madd(float a, float b, float c) { return a * b + c; }
+#else
+__device__ __forceinline__ float madd(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+#endif
 // Same association as the oracle's pinned dot(): ((x*x + y*y) + z*z)
-__device__ __forceinline__ float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ float dot3(V3 a, V3 b) { return madd(a.z, b.z, madd(a.y, b.y, __fmul_rn(a.x, b.x))); }
+// a * s + b
+__device__ __forceinline__ V3 axpy3(V3 a, float s, V3 b) { return mk(madd(a.x, s, b.x), madd(a.y, s, b.y), madd(a.z, s, b.z)); }
 #if RT_STRICT
 // GLSL normalize / divide / pow exactly as the oracle pins them (IEEE sqrt and divide, libm-grade powf)
 __device__ __forceinline__ V3 normalize3(V3 v) { float l = sqrtf(dot3(v, v)); return mk(v.x / l, v.y / l, v.z / l); }
@@ -94,12 +107,13 @@ __device__ __forceinline__ float fpow(float x, float y) {
     return (y == 0.0f) ? 1.0f : r;
 }
 #endif
-__device__ __forceinline__ V3 reflect3(V3 I, V3 N) { float d2 = 2.0f * dot3(N, I); return I - d2 * N; }
+__device__ __forceinline__ V3 reflect3(V3 I, V3 N) { float d2 = __fmul_rn(2.0f, dot3(N, I)); return axpy3(N, -d2, I); }   // I - d2 * N
 __device__ __forceinline__ V3 refract3(V3 I, V3 N, float eta) {
     float ni = dot3(N, I);
-    float k = 1.0f - eta * eta * (1.0f - ni * ni);
+    float k = madd(-__fmul_rn(eta, eta), madd(-ni, ni, 1.0f), 1.0f);          // 1 - eta * eta * (1 - ni * ni)
     if (k < 0.0f) return mk(0.0f, 0.0f, 0.0f);
-    return eta * I - (eta * ni + sqrtf(k)) * N;
+    const float c = madd(eta, ni, sqrtf(k));
+    return axpy3(N, -c, mk(__fmul_rn(eta, I.x), __fmul_rn(eta, I.y), __fmul_rn(eta, I.z)));      // eta * I - c * N
 }
 __device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float sqrt_approx(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
@@ -902,6 +916,7 @@ __device__ __forceinline__ void candidate_test(const RtParams& P, RaySet& rs, in
         unsigned m = 0u;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
+            if (r > 0 && !((want >> r) & 1u)) continue;       // warp-uniform (one ray per lane: slot 0 only)
             if (r == 0 || !shared) so = sphere_origin(cc, rs.o[r]);
             const bool live = rs.best[r] >= live_min && ((want >> r) & 1u);
             if (COUNT) cnt.cull_tests += live;
@@ -934,6 +949,7 @@ __device__ __forceinline__ void candidate_test(const RtParams& P, RaySet& rs, in
         // the discriminant of glsl:591, then the roots, ray slot by ray slot
 #pragma unroll
         for (int r = 0; r < R; ++r) {
+            if (r > 0 && !((want >> r) & 1u)) continue;       // warp-uniform
             if (r == 0 || !shared) so = sphere_origin(cc, rs.o[r]);
             const bool live = rs.best[r] >= live_min && ((want >> r) & 1u);
             if (COUNT) cnt.cull_tests += live;
@@ -963,7 +979,7 @@ template <bool SMEM, bool COUNT, int NC>
 __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
                                           float grow, float live_min, float pad1, float pad2, bool shared, const V3* __restrict__ o_in,
                                           const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
-                                          RtCounters& cnt) {
+                                          RtCounters& cnt, unsigned want = 7u) {
     constexpr int R = kShadowBatch;
     RaySet rs;
     rayset_load(rs, o_in, d_in, best_io, bidx_io);
@@ -1031,7 +1047,7 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
                     const int idx = i + __ffs(mask) - 1;
                     mask &= mask - 1u;
                     const float4 cc = lds128(ra + (uint32_t)idx * 16u);
-                    candidate_test<COUNT>(P, rs, hot0 + idx, cc, shared, live_min, 7u, cnt);
+                    candidate_test<COUNT>(P, rs, hot0 + idx, cc, shared, live_min, want, cnt);
                 }
             }
         }
@@ -1266,6 +1282,59 @@ __device__ __forceinline__ bool shadow_cones(const WarpCtx& w, const V3 (&lp)[kS
 }
 
 // -------------------------------------------------------------------------
+// Secondary rays (the reflection / refraction children of glsl:988-1027) as packets.  One ray per lane, origins
+// and directions differ from lane to lane, but the children of neighbouring pixels that hit the same face
+// leave almost parallel from almost the same place.  Lanes are grouped greedily around a leader (direction
+// within kGroupCos of the leader's, origin within sqrt(rg2) of it); a group is traced as ONE packet: a cone
+// from the groups's mean origin around its mean direction with every bounding radius grown by the distance of
+// the farthest group origin from that apex (a ray shifted to the apex moves by at most that much).  Still every
+// object for every group, in order -- 64 objects per trip instead of one per ray.  At most kMaxGroups groups;
+// lanes left over are returned (true) for the per-ray loops.  A ray with a zero or NaN direction (refract()'s
+// total internal reflection, glsl:1023) misses everything in the per-ray loops too and is dropped here.
+// -------------------------------------------------------------------------
+constexpr float kGroupCos = 0.99f;
+constexpr int kMaxGroups = 12;
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ bool secondary_packets(const RtParams& P, WarpCtx& w, bool act, V3 o, V3 d, float rg2, float pad1, float pad2,
+                                                  float& best, int& bidx, RtCounters& cnt) {
+    const float l2 = dot3(d, d);
+    bool todo = act && l2 > 0.0f && l2 < 1e30f;
+    const V3 u = d * rsqrtf(l2);
+    for (int round = 0; round < kMaxGroups; ++round) {
+        const unsigned rem = __ballot_sync(kFull, todo);
+        if (rem == 0u) break;
+        const int lead = __ffs(rem) - 1;
+        const V3 lu = mk(__shfl_sync(kFull, u.x, lead), __shfl_sync(kFull, u.y, lead), __shfl_sync(kFull, u.z, lead));
+        const V3 lo = mk(__shfl_sync(kFull, o.x, lead), __shfl_sync(kFull, o.y, lead), __shfl_sync(kFull, o.z, lead));
+        const V3 dl = o - lo;
+        const bool in_g = todo && (w.lane == lead || (dot3(u, lu) >= kGroupCos && dot3(dl, dl) <= rg2));
+        float acc[7] = {in_g ? u.x : 0.0f, in_g ? u.y : 0.0f, in_g ? u.z : 0.0f, in_g ? o.x : 0.0f, in_g ? o.y : 0.0f, in_g ? o.z : 0.0f, in_g ? 1.0f : 0.0f};
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+            for (int c = 0; c < 7; ++c) acc[c] += __shfl_xor_sync(kFull, acc[c], off);
+        }
+        Cone gc[1];
+        const float inv_n = 1.0f / acc[6];
+        gc[0].apex = mk(acc[3] * inv_n, acc[4] * inv_n, acc[5] * inv_n);
+        gc[0].axis = normalize3(mk(acc[0], acc[1], acc[2]));
+        const V3 x = cross3(gc[0].axis, u);
+        const V3 da = o - gc[0].apex;
+        const float s2 = warp_max_nonneg(in_g ? fminf(__fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z))), 1.0f) : 0.0f);
+        const float ro2 = warp_max_nonneg(in_g ? dot3(da, da) : 0.0f);
+        cone_close(gc[0], s2, 1e18f);
+        const float grow = __fmaf_rn(sqrt_approx(ro2), 1.001f, pad1);
+        V3 o3[kShadowBatch] = {o, o, o}, d3[kShadowBatch] = {d, d, d};
+        float b3[kShadowBatch] = {in_g ? kFar : 0.0f, 0.0f, 0.0f};
+        int i3[kShadowBatch] = {-1, -1, -1};
+        packet_trace<SMEM, COUNT, 1>(P, w, gc, 1u, grow, 1e-45f, pad1, pad2, false, o3, d3, b3, i3, cnt, 1u);
+        if (COUNT && w.lane == 0) cnt.group_passes++;
+        if (in_g) { best = b3[0]; bidx = i3[0]; todo = false; }
+    }
+    return todo;
+}
+
+// -------------------------------------------------------------------------
 // Closest-hit record: everything ads_phong_lighting and the bounce phases need
 // (glsl:561-573 Collision + the object's material).
 // -------------------------------------------------------------------------
@@ -1275,6 +1344,17 @@ struct Hit {
     int obj;
 };
 
+// One row of mat4 * vec4(v, 1) / mat4 * vec4(v, 0) with the shader's association ((m0 x + m1 y) + m2 z) + m3 w.
+__device__ __forceinline__ float row_pt(const float* __restrict__ m, V3 v) {
+    return __fadd_rn(madd(m[2], v.z, madd(m[1], v.y, __fmul_rn(m[0], v.x))), m[3]);
+}
+__device__ __forceinline__ float row_dir(const float* __restrict__ m, V3 v) {
+#if RT_STRICT
+    return __fadd_rn(madd(m[2], v.z, madd(m[1], v.y, __fmul_rn(m[0], v.x))), __fmul_rn(m[3], 0.0f));
+#else
+    return madd(m[2], v.z, madd(m[1], v.y, __fmul_rn(m[0], v.x)));
+#endif
+}
 // Re-evaluates the winning primitive to produce p, n, inside (glsl:627-637 sphere,
 // glsl:686-721 box).  t is the value the trace loop accepted.
 template <bool SMEM, bool CULL>
@@ -1290,7 +1370,7 @@ __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const WarpCtx& w, 
         (void)sphere_t(sphere_origin(c, o), d, ray_q(d), inside);
         h.obj = __ldg(P.sph_obj + j);
         h.inside = inside;
-        h.p = o + t * d;                                            // glsl:628
+        h.p = axpy3(d, t, o);                                       // glsl:628
         h.n = normalize3(mk(h.p.x - c.x, h.p.y - c.y, h.p.z - c.z));  // glsl:631
         if (inside) h.n = h.n * -1.0f;                              // glsl:634-637
         return h;
@@ -1310,24 +1390,18 @@ __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const WarpCtx& w, 
     // ray in the box's (unscaled) local space, as the shader computes it (glsl:655-656)
     const float* m4 = c->w2l;
     V3 rs, rd;
-    rs.x = ((m4[0] * o.x + m4[1] * o.y) + m4[2] * o.z) + m4[3] * 1.0f;
-    rs.y = ((m4[4] * o.x + m4[5] * o.y) + m4[6] * o.z) + m4[7] * 1.0f;
-    rs.z = ((m4[8] * o.x + m4[9] * o.y) + m4[10] * o.z) + m4[11] * 1.0f;
-    rd.x = ((m4[0] * d.x + m4[1] * d.y) + m4[2] * d.z) + m4[3] * 0.0f;
-    rd.y = ((m4[4] * d.x + m4[5] * d.y) + m4[6] * d.z) + m4[7] * 0.0f;
-    rd.z = ((m4[8] * d.x + m4[9] * d.y) + m4[10] * d.z) + m4[11] * 0.0f;
+    rs = mk(row_pt(m4, o), row_pt(m4 + 4, o), row_pt(m4 + 8, o));
+    rd = mk(row_dir(m4, d), row_dir(m4 + 4, d), row_dir(m4 + 8, d));
     const float rdf = face == 0 ? rd.x : (face == 1 ? rd.y : rd.z);
     V3 nl = mk(face == 0 ? 1.0f : 0.0f, face == 1 ? 1.0f : 0.0f, face == 2 ? 1.0f : 0.0f);   // glsl:707-708
     if (rdf > 0.0f) nl = nl * -1.0f;                                // glsl:712-715
     const float* m = c->nmat;                                       // glsl:718, column-major
-    h.n.x = (m[0] * nl.x + m[3] * nl.y) + m[6] * nl.z;
-    h.n.y = (m[1] * nl.x + m[4] * nl.y) + m[7] * nl.z;
-    h.n.z = (m[2] * nl.x + m[5] * nl.y) + m[8] * nl.z;
-    const V3 ql = rs + t * rd;                                      // glsl:721
+    h.n.x = madd(m[6], nl.z, madd(m[3], nl.y, __fmul_rn(m[0], nl.x)));
+    h.n.y = madd(m[7], nl.z, madd(m[4], nl.y, __fmul_rn(m[1], nl.x)));
+    h.n.z = madd(m[8], nl.z, madd(m[5], nl.y, __fmul_rn(m[2], nl.x)));
+    const V3 ql = axpy3(rd, t, rs);                                 // glsl:721
     const float* l = c->l2w;
-    h.p.x = ((l[0] * ql.x + l[1] * ql.y) + l[2] * ql.z) + l[3] * 1.0f;
-    h.p.y = ((l[4] * ql.x + l[5] * ql.y) + l[6] * ql.z) + l[7] * 1.0f;
-    h.p.z = ((l[8] * ql.x + l[9] * ql.y) + l[10] * ql.z) + l[11] * 1.0f;
+    h.p = mk(row_pt(l, ql), row_pt(l + 4, ql), row_pt(l + 8, ql));
     return h;
 }
 
@@ -1364,8 +1438,9 @@ __device__ __forceinline__ V3 primary_dir(const RtParams& P, const RtCameraDev* 
     float s[4], e[4];
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
-        s[r] = ((m[r] * vx + m[4 + r] * vy) + m[8 + r] * 0.5f) + m[12 + r] * 1.0f;
-        e[r] = ((m[r] * vx + m[4 + r] * vy) + m[8 + r] * 1.0f) + m[12 + r] * 1.0f;
+        const float xy = madd(m[4 + r], vy, __fmul_rn(m[r], vx));                  // (m0 vx + m1 vy)
+        s[r] = __fadd_rn(madd(m[8 + r], 0.5f, xy), m[12 + r]);                      // ... + m2 * 0.5 + m3 * 1
+        e[r] = __fadd_rn(__fadd_rn(xy, m[8 + r]), m[12 + r]);                       // ... + m2 * 1 + m3 * 1
     }
     V3 ws = mk(fdiv(s[0], s[3]), fdiv(s[1], s[3]), fdiv(s[2], s[3]));
     V3 we = mk(fdiv(e[0], e[3]), fdiv(e[1], e[3]), fdiv(e[2], e[3]));
@@ -1417,11 +1492,23 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
         }
         // PHASE 0 (glsl:956-967)
         bool root_sb = false;       // root node whose shadow rays the caller has traced (root_shadows)
+        const bool first_now = have_first;
         if (have_first) {           // warp-uniform: the root ray was traced by the caller
             if (act) { best[0] = first_t; bidx[0] = first_idx; }
             have_first = false;
             root_sb = have_sb;
-        } else {
+        }
+        if (!RT_STRICT && REPACK && CULL) {
+            bool todo = act && !first_now;      // lanes whose ray goes through the per-ray loops
+            if (!first_now && P.packet && P.group_k > 0.0f)
+                todo = secondary_packets<SMEM, COUNT>(P, w, act, o[0], d[0], pk_pad2 * 2.5e5f * P.group_k, pk_pad1, pk_pad2, best[0], bidx[0], cnt);
+            if (__any_sync(kFull, todo)) {
+                float b1 = todo ? kFar : 0.0f; int i1 = -1;
+                if (COUNT && w.lane == 0) cnt.loop_passes++;
+                trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, o[0], d[0], b1, i1, cnt);
+                if (todo) { best[0] = b1; bidx[0] = i1; }
+            }
+        } else if (!first_now) {
             trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, o[0], d[0], best[0], bidx[0], cnt);
         }
         const bool hit = act && bidx[0] >= 0;
@@ -1503,7 +1590,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                 if (n_slots == 0) break;
                 V3 so = mk(0.0f, 0.0f, 0.0f), sd[kShadowBatch];
                 float sb[kShadowBatch];
-                if (shade) so = h.p + h.n * 0.01f;                                  // glsl:808
+                if (shade) so = axpy3(h.n, 0.01f, h.p);                                  // glsl:808
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     if (shade && r < n_slots) {
@@ -1530,12 +1617,43 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                     }
                     Cone cone[kShadowBatch];
                     unsigned on;
-                    if (shadow_cones(w, lp, sd, sb, cone, on)) {
-                        int unused[kShadowBatch] = {-1, -1, -1};
-                        V3 so3[kShadowBatch] = {so, so, so};
-                        packet_trace<SMEM, COUNT, kShadowBatch>(P, w, cone, on, 0.0101f, 1.0f, pk_pad1, pk_pad2, true, so3, sd, sb, unused, cnt);
-                        traced = true;
+                    // One pass when the warp's hit points are coherent; else (hit points of bounce rays scattered
+                    // over the scene) groups of neighbouring hit points around a leader, one pass per group; lanes
+                    // left over after kMaxGroups, or whose group sits too close to a light, take the per-ray loops.
+                    const float rg2 = pk_pad2 * 2.5e5f * P.group_k;
+                    bool todo = shade, left = false;
+                    for (int round = 0; round < kMaxGroups; ++round) {
+                        const unsigned rem = __ballot_sync(kFull, todo);
+                        if (rem == 0u) break;
+                        bool in_g = todo;
+                        if (round > 0) {
+                            const int lead = __ffs(rem) - 1;
+                            const V3 dl = mk(h.p.x - __shfl_sync(kFull, h.p.x, lead), h.p.y - __shfl_sync(kFull, h.p.y, lead),
+                                             h.p.z - __shfl_sync(kFull, h.p.z, lead));
+                            in_g = todo && (w.lane == lead || dot3(dl, dl) <= rg2);
+                        }
+                        float sbg[kShadowBatch];
+#pragma unroll
+                        for (int r = 0; r < kShadowBatch; ++r) sbg[r] = in_g ? sb[r] : 0.0f;
+                        if (shadow_cones(w, lp, sd, sbg, cone, on)) {
+                            int unused[kShadowBatch] = {-1, -1, -1};
+                            V3 so3[kShadowBatch] = {so, so, so};
+                            packet_trace<SMEM, COUNT, kShadowBatch>(P, w, cone, on, 0.0101f, 1.0f, pk_pad1, pk_pad2, true, so3, sd, sbg, unused, cnt);
+                            if (COUNT && w.lane == 0 && round > 0) cnt.group_passes++;      // round 0 is the whole warp
+                            if (in_g) {
+#pragma unroll
+                                for (int r = 0; r < kShadowBatch; ++r) sb[r] = sbg[r];
+                            }
+                            todo = todo && !in_g;
+                        } else if (round > 0) {
+                            left = left || in_g;
+                            todo = todo && !in_g;
+                        }
+                        if (!(P.group_k > 0.0f)) break;         // grouping switched off: the whole warp or nothing
                     }
+                    // lanes already traced and not occluded are traced again by the per-ray loops below (same outcome)
+                    traced = !__any_sync(kFull, todo || left);
+                    if (COUNT && !traced && w.lane == 0) cnt.loop_passes++;
                 }
                 if (traced) {}
                 else if (REPACK && CULL && P.n_lit > 0) trace_shadow<SMEM, REPACK, COUNT, CULL, true>(P, w, so, sd, sb, n_slots, cnt);
@@ -1567,7 +1685,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             if (shade) color = color + wp * phong;
             // PHASES 2-3: each child ray is pushed with its product weight
             if (refracted) {                                                                        // glsl:1010-1027
-                const V3 ro = h.p - h.n * 0.001f;
+                const V3 ro = axpy3(h.n, -0.001f, h.p);
                 // glsl:1013-1020: ratio = 1 / ior, inverted again when leaving the object; both IEEE
                 // quotients are per-object constants, built by the prologue
                 const float ratio = h.inside ? mat->ior_back : mat->inv_ior;
@@ -1578,7 +1696,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                 ++sp;
             }
             if (reflected) {                                                                        // glsl:988-994
-                const V3 ro = h.p + h.n * 0.001f;
+                const V3 ro = axpy3(h.n, 0.001f, h.p);
                 const V3 rdv = reflect3(d[0], h.n);
                 stk[sp][0] = ro.x; stk[sp][1] = ro.y; stk[sp][2] = ro.z;
                 stk[sp][3] = rdv.x; stk[sp][4] = rdv.y; stk[sp][5] = rdv.z;
@@ -1661,7 +1779,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     }
 
     RtCounters cnt;
-    cnt.packet_tests = 0ull;
+    cnt.packet_tests = cnt.group_passes = cnt.loop_passes = 0ull;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
     cnt.cull_tests = cnt.warp_iters = 0ull;
 
@@ -1771,7 +1889,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                             if (P.max_depth > 0 && mat->transparency > 0.0f) wp = wp * (1.0f - mat->transparency);
                             shade = wp != 0.0f;
                             p = h.p;
-                            so = h.p + h.n * 0.01f;                                            // glsl:808
+                            so = axpy3(h.n, 0.01f, h.p);                                            // glsl:808
                         }
                         if (q == 0) { hp[0] = p; so3[0] = so; sh[0] = shade; }
                         else if (q == 1) { hp[1] = p; so3[1] = so; sh[1] = shade; }
@@ -1872,10 +1990,10 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     if (COUNT) {
         // warp-reduce then one atomic per warp per counter
         if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
-        unsigned long long v[11] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
-                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests};
+        unsigned long long v[13] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes};
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
+        for (int k = 0; k < 13; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
     const int n_lights_b = (P.n_lit_batch > 0 && P.n_lit_batch <= kShadowBatch) ? P.n_lit_batch : 0;    // CTA-uniform
 
     RtCounters cnt;
-    cnt.packet_tests = 0ull;
+    cnt.packet_tests = cnt.group_passes = cnt.loop_passes = 0ull;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
     cnt.cull_tests = cnt.warp_iters = 0ull;
 
@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                         if (P.max_depth > 0 && mat->transparency > 0.0f) wp = wp * (1.0f - mat->transparency);
                         shade = wp != 0.0f;
                         p = h.p;
-                        so = h.p + h.n * 0.01f;                                            // glsl:808
+                        so = axpy3(h.n, 0.01f, h.p);                                            // glsl:808
                     }
                     if (q == 0) { hp[0] = p; so3[0] = so; sh[0] = shade; }
                     else if (q == 1) { hp[1] = p; so3[1] = so; sh[1] = shade; }
@@ -560,10 +560,10 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
 
     if (COUNT) {
         if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
-        unsigned long long v[11] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
-                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests};
+        unsigned long long v[13] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes};
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
+        for (int k = 0; k < 13; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

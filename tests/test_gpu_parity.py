@@ -207,6 +207,14 @@ def test_bounding_sphere_test_changes_nothing(tracer, n, w, h, depth):
     assert np.array_equal(on, warp_img)
     assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=8))
     assert st_blk["rays"] == st_warp["rays"] and 0 < st_blk["packet_tests"] < st_warp["packet_tests"]
+    # bit 5: shadow packets without their fan planes; bit 6: bounce rays (depth > 0) traced ray by ray instead of
+    # as grouped packets -- alone and combined with the block / warp kernels
+    for mode in (32, 16 | 32, 64, 8 | 64, 16 | 64, 16 | 32 | 64):
+        assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=mode)), mode
+    _, st_nogrp = tracer.render(sc, cam, w, h, want_stats=True, no_cull=64)
+    assert st_nogrp["group_passes"] == 0 and st_nogrp["rays"] == st_on["rays"]
+    if depth > 0:
+        assert st_on["group_passes"] > 0 and st_on["cull_tests"] < st_nogrp["cull_tests"]
     _, st_ray = tracer.render(sc, cam, w, h, want_stats=True, no_cull=4)
     assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
     assert st_off["cull_tests"] == 0 and st_on["cull_tests"] > 0
@@ -310,7 +318,7 @@ def test_bounding_sphere_test_far_and_tiny_objects(tracer):
     for half in (11.0, 3000.0):
         sc = _far_scene(half)
         on = tracer.render(sc, cam, 320, 180)
-        for mode in (1, 2, 4, 6, 8, 16):
+        for mode in (1, 2, 4, 6, 8, 16, 16 | 32, 64, 8 | 64):
             assert np.array_equal(on, tracer.render(sc, cam, 320, 180, no_cull=mode)), mode
         ref = ob.render(sc, cam, 320, 180)
         _check(tracer.render(sc, cam, 320, 180, strict=True), ref, "far/tiny objects strict", need_edges=False)
