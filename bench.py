@@ -51,14 +51,15 @@ WORKLOADS = {
     "scaled_16k_1080p_d0": ("scaled", 16384, 1920, 1080, 1, 0),
     "scaled_64k_1080p_d0": ("scaled", 65536, 1920, 1080, 1, 0),
     "scaled_1k_1080p_d2": ("scaled", 1024, 1920, 1080, 1, 2),
+    "scaled_16k_1080p_d2": ("scaled", 16384, 1920, 1080, 1, 2),
     # BASELINE config 5: 256 turntable poses at 1024x1024, whole frames sharded over the ranks
     "batch256_1024_d4": ("batch", 5, 1024, 1024, 1, 4),
 }
 BATCH_FRAMES = 256
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel, from the committed
 # `ncu --set full` captures (profiles/r1_ncu_full_*.txt); the 8.3 MB frame mostly stays in the 126 MB L2.
-NCU_DRAM_BYTES = {"builtin_1080p_d4": 58624 + 1224192, "scaled_1k_1080p_d0": 10005760 + 132145152,
-                  "scaled_64k_1080p_d0": 12879104 + 117420544}
+NCU_DRAM_BYTES = {"builtin_1080p_d4": 58624 + 1224192, "scaled_1k_1080p_d0": 8190976 + 164207360,
+                  "scaled_64k_1080p_d0": 11580672 + 160993280}
 DEFAULT_WORKLOAD = "builtin_1080p_d4"
 METRIC = "Mrays/s (rays x bounces)"
 UNIT = "Mrays/s"
@@ -74,7 +75,7 @@ F_BOX, F_SPH, F_HIT, F_LIGHT, F_PRIMARY = 59.0, 41.0, 45.0, 95.0, 76.0
 F_CULL, F_SPH_ROOTS = 12.0, 24.0
 # Packet (cone) test of one object against one cone, one object per lane:
 # v = c - apex 3, h = v.axis 5, v x axis 9, p^2 5, rhs 2, far 1, three products 3, h^2 + p^2 2, compares 3.
-F_PACKET = 33.0
+F_PACKET = 26.0   # v 3, h 5, |v|^2 5, p^2 4, rhs 2, far 1, three products, three compares
 
 
 def algorithmic_flops(st, samples):
@@ -410,7 +411,7 @@ def run_gpu(args, wl_name, wl):
                          "packet_cone_tests": int(st.get("packet_tests", 0)),
                          "lane_use": st["nodes"] / max(1, 32 * st["warp_iters"]),
                          "flops_per_unit": "slab test 59, sphere 41 (24 after its discriminant), bounding-sphere / "
-                                           "discriminant test 12, packet cone test 33 per (object, cone), hit resolve 45, "
+                                           "discriminant test 12, packet cone test 26 per (object, cone), hit resolve 45, "
                                            "shaded light 95, primary ray 76; executed tests only"},
             "clocks": clocks,
         }

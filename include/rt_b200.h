@@ -114,8 +114,10 @@ typedef struct rt_stats {
     uint64_t cull_tests;      /* bounding-sphere / discriminant tests executed for live rays (large scenes) */
     uint64_t warp_iters;      /* bounce-loop iterations summed over warps; nodes/(32*warp_iters) = lane use */
     uint64_t packet_tests;    /* (object, cone) tests of the packet loops, one object per lane (large scenes) */
-    uint64_t group_passes;    /* bounce rays: passes over the scene made for a group of rays / hit points (per warp) */
+    uint64_t group_passes;    /* bounce rays: passes over the scene made for a group of rays (per warp) */
     uint64_t loop_passes;     /* bounce rays: passes made by the per-ray loops for what the groups left over (per warp) */
+    uint64_t candidates;      /* objects that passed a packet test and went through the per-ray tests (per warp) */
+    uint64_t shadow_group_passes;      /* bounce rays: passes made for a group of neighbouring hit points' shadow rays (per warp) */
 } rt_stats;
 
 /* Extended options; zero-initialise then override (rt_options_default()). The

@@ -77,6 +77,8 @@ struct RtCounters {
     unsigned long long packet_tests; /* (object, cone) tests of the packet loops, one per lane (large-scene kernels) */
     unsigned long long group_passes; /* per warp (lane 0): passes over the scene for a group of bounce rays / their hit points */
     unsigned long long loop_passes;  /* per warp (lane 0): per-ray loop passes for bounce rays the groups left over */
+    unsigned long long candidates;   /* per warp (lane 0): candidate_test calls */
+    unsigned long long shadow_group_passes;   /* per warp (lane 0): passes for the shadow rays of a group of hit points */
 };
 
 struct RtParams {
@@ -111,7 +113,8 @@ struct RtParams {
     int32_t blist_stride;
     const float* extent;        /* scene extent E (max |centre| + radius over objects and lights), written by the prologue */
     int32_t fan;                /* 1: shadow packets of the block kernel also carry a fan plane (rt_kernel.cuh: Cone::nrm) */
-    float group_k;              /* > 0: secondary rays are traced as grouped packets; group radius^2 = E^2 * group_k, group_k = n_hot^(-2/3) */
+    float group_cos;            /* bounce rays join a group when their direction is within this cosine of the leader's */
+    float group_k;              /* > 0: secondary rays are traced as grouped packets; group radius^2 = E^2 * group_k */
     uint32_t* blk_log;          /* block kernel, instrumented twin only (RT_BLOCK_LOG=path): 16 words per block, see tools/block_log.py */
 };
 

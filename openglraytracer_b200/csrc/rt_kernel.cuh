@@ -813,7 +813,7 @@ __device__ __forceinline__ void lights_tile(const RtParams& P, const float4* __r
 // above, so a frame is byte-identical with the packet tests on or off (tests/test_gpu_parity.py).
 // -------------------------------------------------------------------------
 struct Cone {
-    V3 apex, axis;    // axis = 0: no angular bound (everything within `reach` of the apex passes the cone part)
+    V3 apex, axis;    // cone_open(): axis = 0, c2 = 0: no angular bound (everything within `reach` of the apex passes the cone part)
     float s, c2;      // padded sin(theta), 1 - s^2
     float reach;      // no ray of the packet extends further than this from the apex
     // Fan: the packet's rays also stay within `hw` of the plane through the apex with unit normal `nrm`.  Shadow
@@ -835,11 +835,14 @@ template <bool SLAB = false>
 __device__ __forceinline__ bool cone_pass(const Cone& k, float4 c, float rp) {
     const V3 v = mk(c.x - k.apex.x, c.y - k.apex.y, c.z - k.apex.z);
     const float h = __fmaf_rn(v.x, k.axis.x, __fmaf_rn(v.y, k.axis.y, __fmul_rn(v.z, k.axis.z)));
-    const V3 x = cross3(v, k.axis);
-    const float p2 = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
+    const float v2 = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
+    // squared distance to the axis as |v|^2 - h^2 (7 instructions fewer than |v x axis|^2; this test is what the
+    // large-scene kernels spend their time in).  The difference cancels, so it is lowered by 2e-6 |v|^2 -- above the
+    // rounding of v2, of h (|axis| = 1 +- 4e-7) and of the FMA together (1.4e-6 |v|^2): never larger than the true
+    // value, so the test stays conservative; far from the apex it is a little less tight (0.0014 |v| in p).
+    const float p2 = __fmaf_rn(-2e-6f, v2, __fmaf_rn(-h, h, v2));
     const float rhs = __fmaf_rn(h, k.s, rp);
     const float far = k.reach + rp;
-    const float v2 = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
     bool pass = rhs >= 0.0f && __fmul_rn(p2, k.c2) <= __fmul_rn(rhs, rhs) && v2 <= __fmul_rn(far, far);
     if (SLAB) {
         const float sl = fabsf(__fmaf_rn(v.x, k.nrm.x, __fmaf_rn(v.y, k.nrm.y, __fmul_rn(v.z, k.nrm.z))));
@@ -854,6 +857,12 @@ __device__ __forceinline__ void cone_close(Cone& k, float s2max, float reach) {
     k.reach = reach;
     k.nrm = mk(0.0f, 0.0f, 0.0f);
     k.hw = 3e38f;
+}
+// No angular bound: everything within `reach` of the apex (and within the fan plane's slab) passes.
+__device__ __forceinline__ void cone_open(Cone& k) {
+    k.axis = mk(0.0f, 0.0f, 0.0f);
+    k.s = 1.0f;
+    k.c2 = 0.0f;
 }
 // Unit normal of the plane through a light and a view axis (a = the axis, b = eye - light); zero when the light
 // sits on the axis (then the cone is narrow anyway).
@@ -912,6 +921,7 @@ __device__ __forceinline__ void candidate_test(const RtParams& P, RaySet& rs, in
     constexpr int R = kShadowBatch;
     const bool anyhit = live_min >= 1.0f;
     SphO so;
+    if (COUNT && (threadIdx.x & 31) == 0) cnt.candidates++;
     if (hot < P.n_box) {
         unsigned m = 0u;
 #pragma unroll
@@ -988,43 +998,64 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
     for (int k = 0; k < NC; ++k) cone[k] = cone_in[k];
     const bool anyhit = live_min >= 1.0f;
     const int lane = w.lane;
-    // resident: each list is one "tile" in shared memory; streaming: kTileSph-record tiles through the warp's double buffer
-    const int nbt = SMEM ? 1 : n_box_tiles<true>(P);
-    const int n_tiles = nbt + (SMEM ? 1 : n_sph_tiles(P));
-    for (int t = 0; t < n_tiles; ++t) {
+    // one cone: two objects per lane and iteration (64 objects per trip, two independent dependency
+    // chains); three cones: one object per lane (the six chains of two would spill)
+    constexpr int kHalves = NC == 1 ? 2 : 1;
+    constexpr int W = 32 * kHalves;                              // objects per trip
+    // Resident: the lists sit in shared memory.  Streamed: the warp's 6 KB of tile buffers are a ring of
+    // trip-sized slots filled by per-lane 16-byte cp.async copies straight from L2, kSlots - 1 trips in
+    // flight (a warp's pass over the scene is latency bound otherwise: one 3 KB tile ahead was not enough).
+    constexpr int kSlots = (2 * kTileBytes) / (W * 16);
+    constexpr int kAhead = kSlots - 1;
+    for (int part = 0; part < 2; ++part) {
         // no live ray left in the warp (shadow rays: every one occluded, glsl:816 needs ANY occluder)
-        if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) {
-            if (t > 0) tile_drain<SMEM>(w, t - 1, n_tiles);
-            break;
+        if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
+        const bool sph = part != 0;
+        const int n = sph ? P.n_sph : P.n_box;
+        if (n == 0) continue;
+        const int hot0 = sph ? P.n_box : 0;
+        const float4* __restrict__ gp = sph ? P.sph_hot : P.box_cull;
+        const uint32_t ra = SMEM ? smem_addr(smem_f4 + (sph ? w.sph_off4 : w.box_off4)) : w.buf_addr[0];
+        auto issue = [&](int trip) {                              // this lane's records of one trip into its ring slot
+            const uint32_t slot = ra + (uint32_t)(trip % kSlots) * (W * 16u);
+#pragma unroll
+            for (int hlf = 0; hlf < kHalves; ++hlf) {
+                const int idx = min(trip * W + hlf * 32 + lane, n - 1);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot + (uint32_t)(hlf * 32 + lane) * 16u), "l"(gp + idx) : "memory");
+            }
+        };
+        if (!SMEM) {
+            __syncwarp();                                         // every lane is done with the ring (previous part / call)
+#pragma unroll 1
+            for (int t = 0; t < kAhead; ++t) {
+                if (t * W < n) issue(t);
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            }
         }
-        const bool sph = t >= nbt;
-        const int base = SMEM ? 0 : (sph ? t - nbt : t) * kTileSph;
-        const int n = SMEM ? (sph ? P.n_sph : P.n_box) : min(kTileSph, (sph ? P.n_sph : P.n_box) - base);
-        const int hot0 = (sph ? P.n_box : 0) + base;
-        uint32_t ra;
-        if (SMEM) {
-            ra = smem_addr(smem_f4 + (sph ? w.sph_off4 : w.box_off4));
-        } else {
-            if (t == 0 && lane == 0) tile_issue<true>(P, w, 0);
-            __syncwarp();                                     // every lane is done reading buffer (t+1)&1 (tile t-1)
-            if (lane == 0 && t + 1 < n_tiles) tile_issue<true>(P, w, t + 1);
-            tile_wait(w, t & 1);
-            ra = w.buf_addr[t & 1];
-        }
-        // one cone: two objects per lane and iteration (64 objects per trip, two independent dependency
-        // chains); three cones: one object per lane (the six chains of two would spill)
-        constexpr int kHalves = NC == 1 ? 2 : 1;
-        for (int i0 = 0; i0 < n; i0 += 32 * kHalves) {
+        int trip = 0;
+        for (int i0 = 0; i0 < n; i0 += W, ++trip) {
             // shadow packets: leave as soon as every ray of the warp is occluded (checked every 256 objects)
             if (anyhit && (i0 & 255) == 0 && i0 > 0 &&
                 !__any_sync(kFull, rs.best[0] >= 1.0f || rs.best[1] >= 1.0f || rs.best[2] >= 1.0f)) break;
+            uint32_t rt;                                          // shared-memory address of record i0
+            if (SMEM) {
+                rt = ra + (uint32_t)i0 * 16u;
+            } else {
+                __syncwarp();                                     // the slot of trip - 1 is free: it takes trip + kAhead
+                if ((trip + kAhead) * W < n) issue(trip + kAhead);
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                asm volatile("cp.async.wait_group %0;" ::"n"(kAhead) : "memory");
+                __syncwarp();                                     // every lane's copies of this trip have landed
+                rt = ra + (uint32_t)(trip % kSlots) * (W * 16u);
+            }
             const int j0 = i0 + lane, j1 = j0 + 32;
-            const float4 c0 = lds128(ra + (uint32_t)min(j0, n - 1) * 16u);
+            const int last = n - 1 - i0;                          // in-trip index of the list's last record
+            const float4 c0 = lds128(rt + (uint32_t)min(lane, last) * 16u);
             const float rp0 = packet_radius(c0.w, sph, grow, pad1, pad2);
             float4 c1 = c0;
             float rp1 = rp0;
             if (kHalves == 2) {
-                c1 = lds128(ra + (uint32_t)min(j1, n - 1) * 16u);
+                c1 = lds128(rt + (uint32_t)min(lane + 32, last) * 16u);
                 rp1 = packet_radius(c1.w, sph, grow, pad1, pad2);
             }
             bool pass0 = false, pass1 = false;
@@ -1042,15 +1073,15 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
 #pragma unroll 1
             for (int half = 0; half < kHalves; ++half) {
                 unsigned mask = half ? mask1 : mask0;
-                const int i = i0 + 32 * half;
                 while (mask) {
-                    const int idx = i + __ffs(mask) - 1;
+                    const int k32 = 32 * half + __ffs(mask) - 1;  // in-trip index
                     mask &= mask - 1u;
-                    const float4 cc = lds128(ra + (uint32_t)idx * 16u);
-                    candidate_test<COUNT>(P, rs, hot0 + idx, cc, shared, live_min, want, cnt);
+                    const float4 cc = lds128(rt + (uint32_t)k32 * 16u);
+                    candidate_test<COUNT>(P, rs, hot0 + i0 + k32, cc, shared, live_min, want, cnt);
                 }
             }
         }
+        if (!SMEM) asm volatile("cp.async.wait_group 0;" ::: "memory");   // nothing of this pass may land later
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) { best_io[r] = rs.best[r]; bidx_io[r] = rs.bidx[r]; }
@@ -1285,14 +1316,13 @@ __device__ __forceinline__ bool shadow_cones(const WarpCtx& w, const V3 (&lp)[kS
 // Secondary rays (the reflection / refraction children of glsl:988-1027) as packets.  One ray per lane, origins
 // and directions differ from lane to lane, but the children of neighbouring pixels that hit the same face
 // leave almost parallel from almost the same place.  Lanes are grouped greedily around a leader (direction
-// within kGroupCos of the leader's, origin within sqrt(rg2) of it); a group is traced as ONE packet: a cone
+// within P.group_cos of the leader's, origin within sqrt(rg2) of it); a group is traced as ONE packet: a cone
 // from the groups's mean origin around its mean direction with every bounding radius grown by the distance of
 // the farthest group origin from that apex (a ray shifted to the apex moves by at most that much).  Still every
 // object for every group, in order -- 64 objects per trip instead of one per ray.  At most kMaxGroups groups;
 // lanes left over are returned (true) for the per-ray loops.  A ray with a zero or NaN direction (refract()'s
 // total internal reflection, glsl:1023) misses everything in the per-ray loops too and is dropped here.
 // -------------------------------------------------------------------------
-constexpr float kGroupCos = 0.99f;
 constexpr int kMaxGroups = 12;
 template <bool SMEM, bool COUNT>
 __device__ __forceinline__ bool secondary_packets(const RtParams& P, WarpCtx& w, bool act, V3 o, V3 d, float rg2, float pad1, float pad2,
@@ -1307,7 +1337,7 @@ __device__ __forceinline__ bool secondary_packets(const RtParams& P, WarpCtx& w,
         const V3 lu = mk(__shfl_sync(kFull, u.x, lead), __shfl_sync(kFull, u.y, lead), __shfl_sync(kFull, u.z, lead));
         const V3 lo = mk(__shfl_sync(kFull, o.x, lead), __shfl_sync(kFull, o.y, lead), __shfl_sync(kFull, o.z, lead));
         const V3 dl = o - lo;
-        const bool in_g = todo && (w.lane == lead || (dot3(u, lu) >= kGroupCos && dot3(dl, dl) <= rg2));
+        const bool in_g = todo && (w.lane == lead || (dot3(u, lu) >= P.group_cos && dot3(dl, dl) <= rg2));
         float acc[7] = {in_g ? u.x : 0.0f, in_g ? u.y : 0.0f, in_g ? u.z : 0.0f, in_g ? o.x : 0.0f, in_g ? o.y : 0.0f, in_g ? o.z : 0.0f, in_g ? 1.0f : 0.0f};
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {
@@ -1639,7 +1669,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                             int unused[kShadowBatch] = {-1, -1, -1};
                             V3 so3[kShadowBatch] = {so, so, so};
                             packet_trace<SMEM, COUNT, kShadowBatch>(P, w, cone, on, 0.0101f, 1.0f, pk_pad1, pk_pad2, true, so3, sd, sbg, unused, cnt);
-                            if (COUNT && w.lane == 0 && round > 0) cnt.group_passes++;      // round 0 is the whole warp
+                            if (COUNT && w.lane == 0 && round > 0) cnt.shadow_group_passes++;      // round 0 is the whole warp
                             if (in_g) {
 #pragma unroll
                                 for (int r = 0; r < kShadowBatch; ++r) sb[r] = sbg[r];
@@ -1779,7 +1809,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     }
 
     RtCounters cnt;
-    cnt.packet_tests = cnt.group_passes = cnt.loop_passes = 0ull;
+    cnt.packet_tests = cnt.group_passes = cnt.loop_passes = cnt.candidates = cnt.shadow_group_passes = 0ull;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
     cnt.cull_tests = cnt.warp_iters = 0ull;
 
@@ -1990,10 +2020,11 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     if (COUNT) {
         // warp-reduce then one atomic per warp per counter
         if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
-        unsigned long long v[13] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
-                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes};
+        unsigned long long v[15] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes,
+                                    cnt.candidates, cnt.shadow_group_passes};
 #pragma unroll
-        for (int k = 0; k < 13; ++k) {
+        for (int k = 0; k < 15; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
     const int n_lights_b = (P.n_lit_batch > 0 && P.n_lit_batch <= kShadowBatch) ? P.n_lit_batch : 0;    // CTA-uniform
 
     RtCounters cnt;
-    cnt.packet_tests = cnt.group_passes = cnt.loop_passes = 0ull;
+    cnt.packet_tests = cnt.group_passes = cnt.loop_passes = cnt.candidates = cnt.shadow_group_passes = 0ull;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
     cnt.cull_tests = cnt.warp_iters = 0ull;
 
@@ -422,7 +422,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     cone_close(lc[k], s2, __fmaf_rn(sqrt_approx(lmax), 1.0001f, 0.0101f));
                     // hit points spread beyond kBlockMinCos as seen from the light: no angular bound, the reach and the
                     // fan plane still hold
-                    if (!k_ok) lc[k].axis = mk(0.0f, 0.0f, 0.0f);
+                    if (!k_ok) cone_open(lc[k]);
                     cone_fan(lc[k], fan_normal(bc[0].axis, org - lp[k]), P.fan ? hmax : 3e38f, pk_pad1);
                     ball[k] = nmax > 0.0f ? __fmaf_rn(sqrt_approx(nmax), 1.0001f, 0.0101f) : 0.0f;
                 }
@@ -489,7 +489,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             if (!use_b && (!narrow || ball_r > 0.0f)) { have_sb = false; break; }
                             cone_close(wc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
                             if (use_b) {
-                                if (!narrow) wc[0].axis = mk(0.0f, 0.0f, 0.0f);           // reach and fan plane only
+                                if (!narrow) cone_open(wc[0]);                            // reach and fan plane only
                                 const float hwp = warp_max_nonneg(hmax < 1e30f ? hmax : 1e30f);
                                 cone_fan(wc[0], wn, P.fan ? hwp : 3e38f, pk_pad1);
                             }
@@ -560,10 +560,11 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
 
     if (COUNT) {
         if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
-        unsigned long long v[13] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
-                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes};
+        unsigned long long v[15] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+                                    cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes,
+                                    cnt.candidates, cnt.shadow_group_passes};
 #pragma unroll
-        for (int k = 0; k < 13; ++k) {
+        for (int k = 0; k < 15; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

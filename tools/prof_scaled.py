@@ -16,8 +16,8 @@ r.upload_scene(sc)
 pk, _ = rt.fp32_peak_tflops(iters=4096)
 for i in range(reps):
     img, st = r.render(None, cam, w, h, want_stats=True, no_cull=no_cull)
-    fl = 59.0 * st["box_tests"] + (24.0 if st["cull_tests"] else 41.0) * st["sphere_tests"] + 12.0 * st["cull_tests"] + 33.0 * st["packet_tests"]
+    fl = 59.0 * st["box_tests"] + (24.0 if st["cull_tests"] else 41.0) * st["sphere_tests"] + 12.0 * st["cull_tests"] + 26.0 * st["packet_tests"]
     print(json.dumps(dict(n=n, w=w, h=h, depth=depth, kernel_ms=st["kernel_ms"], tflops=fl / st["kernel_ms"] / 1e9,
                           frac=fl / st["kernel_ms"] / 1e9 / pk, peak=pk, mrays=st["rays"] / st["kernel_ms"] / 1e3,
-                          box_tests=st["box_tests"], sph_tests=st["sphere_tests"], cull_tests=st["cull_tests"], packet_tests=st["packet_tests"], rays=st["rays"], nodes=st["nodes"], warp_iters=st["warp_iters"], group_passes=st.get("group_passes", 0), loop_passes=st.get("loop_passes", 0),
+                          box_tests=st["box_tests"], sph_tests=st["sphere_tests"], cull_tests=st["cull_tests"], packet_tests=st["packet_tests"], rays=st["rays"], nodes=st["nodes"], warp_iters=st["warp_iters"], group_passes=st.get("group_passes", 0), loop_passes=st.get("loop_passes", 0), candidates=st.get("candidates", 0), shadow_group_passes=st.get("shadow_group_passes", 0),
                           lane_use=st["nodes"] / max(1, 32 * st["warp_iters"]), no_cull=no_cull)))
