@@ -203,7 +203,7 @@ int rt_render_uploaded(rt_context* ctx, const rt_camera* cameras, int n_frames,
 #define RT_PROLOGUE_AUTO   0
 #define RT_PROLOGUE_HOST   1
 #define RT_PROLOGUE_DEVICE 2
-#define RT_PROLOGUE_DEVICE_MIN_OBJECTS 2048
+#define RT_PROLOGUE_DEVICE_MIN_OBJECTS 512
 int rt_set_prologue(rt_context* ctx, int mode);
 
 /* The shader's hard-coded data as a function of its one real uniform `time`

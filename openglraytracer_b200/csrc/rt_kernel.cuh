@@ -809,7 +809,7 @@ __device__ __forceinline__ void lights_tile(const RtParams& P, const float4* __r
 // Conservative by construction: a ray of the packet can only hit an object
 // whose bounding sphere, grown by `rp`'s padding, meets the cone: signed distance of the centre to the
 // cone's surface, p*cos(theta) - h*sin(theta) <= rp, with sin(theta) padded by 5e-4 relative + 4e-6
-// and p^2 = |v x axis|^2 (no cancellation).  The per-ray tests behind it are the ones of the loops
+// and p^2 = |v|^2 - h^2 lowered by its rounding bound.  The per-ray tests behind it are the ones of the loops
 // above, so a frame is byte-identical with the packet tests on or off (tests/test_gpu_parity.py).
 // -------------------------------------------------------------------------
 struct Cone {
