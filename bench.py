@@ -58,8 +58,8 @@ WORKLOADS = {
 BATCH_FRAMES = 256
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel, from the committed
 # `ncu --set full` captures (profiles/r1_ncu_full_*.txt); the 8.3 MB frame mostly stays in the 126 MB L2.
-NCU_DRAM_BYTES = {"builtin_1080p_d4": 58624 + 1224192, "scaled_1k_1080p_d0": 8190976 + 164207360,
-                  "scaled_64k_1080p_d0": 11580672 + 160993280}
+NCU_DRAM_BYTES = {"builtin_1080p_d4": 58624 + 1224192, "scaled_1k_1080p_d0": 8672512 + 167796736,
+                  "scaled_64k_1080p_d0": 11898368 + 177194752}
 DEFAULT_WORKLOAD = "builtin_1080p_d4"
 METRIC = "Mrays/s (rays x bounces)"
 UNIT = "Mrays/s"

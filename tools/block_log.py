@@ -4,7 +4,7 @@ RT_BLOCK_LOG=path makes the instrumented twin write one 16-word record per block
   [0,1] start (globaltimer ns)  [2] ns until list A is complete  [3] list A entries  [4] list B entries
   [5] flags: 1 use_b, 2 !use_b, 4 use_a, 8 !use_a, bits 4-6 light cones on, bits 8-10 balls
   [6] SM id  [7] CTA  [8..15] ns from block start until warp k reached the end of its work item
-Usage: python tools/block_log.py n_objects [width height depth]
+Usage: python tools/block_log.py n_objects [width height depth]   |   python tools/block_log.py --analyze log.bin
 """
 import os
 import sys
@@ -13,14 +13,16 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-import openglraytracer_b200 as rt  # noqa: E402
 
 
 def main():
+    if len(sys.argv) > 2 and sys.argv[1] == "--analyze":          # summarise an existing log (no GPU needed)
+        return analyze(sys.argv[2])
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
     w = int(sys.argv[2]) if len(sys.argv) > 2 else 1920
     h = int(sys.argv[3]) if len(sys.argv) > 3 else 1080
     depth = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+    import openglraytracer_b200 as rt
     path = os.path.join(ROOT, "gpurun_out", "block_log_%d.bin" % n)
     os.makedirs(os.path.dirname(path), exist_ok=True)
     os.environ["RT_BLOCK_LOG"] = path
@@ -30,6 +32,10 @@ def main():
         r.render(sc, cam, w, h)
         img, st = r.render(sc, cam, w, h, want_stats=True)
     print("kernel_ms", st["kernel_ms"])
+    analyze(path)
+
+
+def analyze(path):
     a = np.fromfile(path, dtype=np.uint32).reshape(-1, 16)
     t0 = a[:, 0].astype(np.uint64) | (a[:, 1].astype(np.uint64) << np.uint64(32))
     ok = t0 > 0
