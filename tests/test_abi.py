@@ -42,6 +42,24 @@ def test_pod_layouts_match_shader_structs():
     assert C.sizeof(rt.Material) == C.sizeof(ob.Material) and C.sizeof(rt.Object) == C.sizeof(ob.Object)
 
 
+def test_ctypes_mirrors_match_the_header(tmp_path):
+    """The ctypes mirrors of rt_stats / rt_options / the scene structs have the sizes (and, for the last field,
+    the offsets) the C compiler gives the declarations in include/rt_b200.h."""
+    import subprocess
+    from openglraytracer_b200 import _abi
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "rt_b200.h"\n'
+                   'int main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(rt_stats), sizeof(rt_options), '
+                   'sizeof(rt_object), sizeof(rt_light), sizeof(rt_camera), sizeof(rt_material), '
+                   'offsetof(rt_stats, shadow_group_passes), offsetof(rt_options, no_cull)); return 0; }\n')
+    exe = tmp_path / "sizes"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    want = [C.sizeof(_abi.Stats), C.sizeof(_abi.Options), C.sizeof(rt.Object), C.sizeof(rt.Light), C.sizeof(rt.Camera),
+            C.sizeof(rt.Material), _abi.Stats.shadow_group_passes.offset, _abi.Options.no_cull.offset]
+    assert got == want
+
+
 @pytest.mark.parametrize("time", [0.0, 0.016, 2.5, 7.123, 100.0])
 def test_builtin_scene_and_camera_match_oracle_restatement(time):
     a, b = rt.builtin_scene(time), ob.builtin_scene(time)
