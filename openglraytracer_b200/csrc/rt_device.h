@@ -32,6 +32,10 @@
 #define RT_PACKET_MIN_OBJECTS 96
 /* from this many hot objects the CTA-level packet tests (rt_kernel_block.cuh) pay for their barriers */
 #define RT_BLOCK_MIN_OBJECTS 128
+/* with bounce rays (depth > 0) and this many hot objects the per-warp kernel is faster again: the bounce work of a
+ * block's 8 work items is uneven and its warps wait for each other at the block's barriers (16k objects, depth 2:
+ * 56 ms against 69 ms) */
+#define RT_BLOCK_MAX_OBJECTS_BOUNCE 4096
 #define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
 
 /* Cold record: 64 words. */

@@ -505,7 +505,9 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     // Packet (cone) tests in front of the per-ray bounding tests; the per-light records are then only a
     // fallback for incoherent packets and are left out (they would halve the resident capacity).
     P.packet = (P.cull && !(o.no_cull & 4) && c->n_box + c->n_sph >= RT_PACKET_MIN_OBJECTS) ? 1 : 0;
-    P.block = (P.packet && !(o.no_cull & 8) && (c->n_box + c->n_sph >= RT_BLOCK_MIN_OBJECTS || (o.no_cull & 16))) ? 1 : 0;
+    const int n_hot_all = c->n_box + c->n_sph;
+    const bool block_pays = n_hot_all >= RT_BLOCK_MIN_OBJECTS && (c->max_depth == 0 || n_hot_all < RT_BLOCK_MAX_OBJECTS_BOUNCE);
+    P.block = (P.packet && !(o.no_cull & 8) && (block_pays || (o.no_cull & 16))) ? 1 : 0;
     P.fan = (P.block && !(o.no_cull & 32)) ? 1 : 0;
     // bounce rays as grouped packets: group radius 0.1 E, directions within 8 degrees of the leader's (measured flat
     // between 0.02 E and 0.14 E and between 2.5 and 25 degrees on the 1k and 16k scenes)
