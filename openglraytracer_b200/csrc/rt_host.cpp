@@ -138,6 +138,17 @@ struct rt_context {
     int depth_copy = 0;
     uint8_t* h_pinned = nullptr;
     size_t h_pinned_cap = 0;
+    // Host prologue: every record array is packed into one page-locked staging block and goes up in ONE copy into
+    // one device arena (ten small pageable copies and a second stream synchronisation were 4 % of the built-in
+    // frame's end-to-end time).  The render reads the arrays through these pointers, whichever prologue wrote them.
+    DevBuf<uint8_t> d_arena;
+    uint8_t* h_stage = nullptr;
+    size_t h_stage_cap = 0;
+    const float *p_box_fast = nullptr, *p_box_strict = nullptr, *p_box_cull = nullptr, *p_obj_lrec = nullptr, *p_sph = nullptr;
+    const int32_t *p_box_obj = nullptr, *p_sph_obj = nullptr;
+    const RtCold* p_cold = nullptr;
+    const RtLightDev* p_lights = nullptr;
+    const unsigned int* p_extent = nullptr;
     // uploaded scene
     bool have_scene = false;
     int n_box = 0, n_sph = 0, n_lights = 0, max_depth = 0, n_lit = 0;
@@ -298,6 +309,8 @@ int rt_destroy(rt_context* c) {
     c->d_objs.release(); c->d_kind.release(); c->d_hot.release(); c->d_extent.release(); c->d_blist.release(); c->d_blklog.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    c->d_arena.release();
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -329,32 +342,37 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     CU(cudaSetDevice(c->device));
     // The previous frame may still be reading these buffers.
     CU(cudaStreamSynchronize(c->stream));
-    CU(c->d_box_fast.reserve(hs.box_fast.size() + 4));
-    CU(c->d_box_strict.reserve(hs.box_strict.size() + 4));
-    CU(c->d_box_cull.reserve(hs.box_cull.size() + 4));
-    CU(c->d_obj_lrec.reserve(hs.obj_lrec.size() + 4));
-    CU(c->d_sph.reserve(hs.sph.size() + 4));
-    CU(c->d_box_obj.reserve(hs.box_obj.size() + 1));
-    CU(c->d_sph_obj.reserve(hs.sph_obj.size() + 1));
-    CU(c->d_cold.reserve(hs.cold.size() + 1));
-    CU(c->d_lights.reserve(hs.lights.size() + 1));
-    CU(c->d_extent.reserve(1));
-    auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
-        if (bytes == 0) return cudaSuccess;
-        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
-    };
-    CU(up(c->d_extent.p, &hs.extent_f, 4));
-    CU(up(c->d_box_fast.p, hs.box_fast.data(), hs.box_fast.size() * 4));
-    CU(up(c->d_box_strict.p, hs.box_strict.data(), hs.box_strict.size() * 4));
-    CU(up(c->d_box_cull.p, hs.box_cull.data(), hs.box_cull.size() * 4));
-    CU(up(c->d_obj_lrec.p, hs.obj_lrec.data(), hs.obj_lrec.size() * 4));
-    CU(up(c->d_sph.p, hs.sph.data(), hs.sph.size() * 4));
-    CU(up(c->d_box_obj.p, hs.box_obj.data(), hs.box_obj.size() * 4));
-    CU(up(c->d_sph_obj.p, hs.sph_obj.data(), hs.sph_obj.size() * 4));
-    CU(up(c->d_cold.p, hs.cold.data(), hs.cold.size() * sizeof(RtCold)));
-    CU(up(c->d_lights.p, hs.lights.data(), hs.lights.size() * sizeof(RtLightDev)));
-    // pageable sources: the copies above are staged before return, but keep it simple and safe
-    CU(cudaStreamSynchronize(c->stream));
+    // layout of the arena: 256-byte aligned sections, 256 bytes of slack after each (pipelined record loads may read
+    // a few records past the end of a list; what they read is never used)
+    struct Sec { const void* src; size_t bytes; size_t off; };
+    Sec sec[10] = {{&hs.extent_f, 4, 0}, {hs.box_fast.data(), hs.box_fast.size() * 4, 0}, {hs.box_strict.data(), hs.box_strict.size() * 4, 0},
+                   {hs.box_cull.data(), hs.box_cull.size() * 4, 0}, {hs.obj_lrec.data(), hs.obj_lrec.size() * 4, 0},
+                   {hs.sph.data(), hs.sph.size() * 4, 0}, {hs.box_obj.data(), hs.box_obj.size() * 4, 0},
+                   {hs.sph_obj.data(), hs.sph_obj.size() * 4, 0}, {hs.cold.data(), hs.cold.size() * sizeof(RtCold), 0},
+                   {hs.lights.data(), hs.lights.size() * sizeof(RtLightDev), 0}};
+    size_t total = 0;
+    for (Sec& x : sec) { x.off = total; total += (x.bytes + 256 + 255) / 256 * 256; }
+    CU(c->d_arena.reserve(total));
+    if (total > c->h_stage_cap) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr; c->h_stage_cap = 0;
+        CU(cudaHostAlloc((void**)&c->h_stage, total + total / 4, cudaHostAllocDefault));
+        c->h_stage_cap = total + total / 4;
+    }
+    // the stream is idle (synchronised above), so the staging block of the previous upload has been consumed
+    for (const Sec& x : sec) if (x.bytes) memcpy(c->h_stage + x.off, x.src, x.bytes);
+    CU(cudaMemcpyAsync(c->d_arena.p, c->h_stage, total, cudaMemcpyHostToDevice, c->stream));
+    uint8_t* a = c->d_arena.p;
+    c->p_extent = reinterpret_cast<const unsigned int*>(a + sec[0].off);
+    c->p_box_fast = reinterpret_cast<const float*>(a + sec[1].off);
+    c->p_box_strict = reinterpret_cast<const float*>(a + sec[2].off);
+    c->p_box_cull = reinterpret_cast<const float*>(a + sec[3].off);
+    c->p_obj_lrec = reinterpret_cast<const float*>(a + sec[4].off);
+    c->p_sph = reinterpret_cast<const float*>(a + sec[5].off);
+    c->p_box_obj = reinterpret_cast<const int32_t*>(a + sec[6].off);
+    c->p_sph_obj = reinterpret_cast<const int32_t*>(a + sec[7].off);
+    c->p_cold = reinterpret_cast<const RtCold*>(a + sec[8].off);
+    c->p_lights = reinterpret_cast<const RtLightDev*>(a + sec[9].off);
     c->n_box = (int)hs.box_obj.size();
     c->n_sph = (int)hs.sph_obj.size();
     c->n_lights = (int)hs.lights.size();
@@ -403,6 +421,9 @@ static int upload_device(rt_context* c, const rt_scene* scene) {
                         c->d_extent.p, c->d_obj_lrec.p, c->stream));
     g_launches += 2 + (hs.n_lit > 0 ? 1 : 0);
     CU(cudaStreamSynchronize(c->stream));   // the host vectors above go out of scope
+    c->p_extent = c->d_extent.p; c->p_box_fast = c->d_box_fast.p; c->p_box_strict = nullptr; c->p_box_cull = c->d_box_cull.p;
+    c->p_obj_lrec = c->d_obj_lrec.p; c->p_sph = c->d_sph.p; c->p_box_obj = c->d_box_obj.p; c->p_sph_obj = c->d_sph_obj.p;
+    c->p_cold = c->d_cold.p; c->p_lights = c->d_lights.p;
     c->n_box = (int)nb;
     c->n_sph = (int)ns;
     c->n_lights = (int)hs.lights.size();
@@ -484,12 +505,12 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
 
     RtParams P;
     memset(&P, 0, sizeof(P));
-    P.box_hot = reinterpret_cast<const float4*>(o.strict ? c->d_box_strict.p : c->d_box_fast.p);
-    P.box_cull = reinterpret_cast<const float4*>(c->d_box_cull.p);
-    P.sph_hot = reinterpret_cast<const float4*>(c->d_sph.p);
-    P.obj_lrec = reinterpret_cast<const float4*>(c->d_obj_lrec.p);
-    P.box_obj = c->d_box_obj.p; P.sph_obj = c->d_sph_obj.p;
-    P.cold = c->d_cold.p; P.lights = c->d_lights.p; P.cams = c->d_cams.p;
+    P.box_hot = reinterpret_cast<const float4*>(o.strict ? c->p_box_strict : c->p_box_fast);
+    P.box_cull = reinterpret_cast<const float4*>(c->p_box_cull);
+    P.sph_hot = reinterpret_cast<const float4*>(c->p_sph);
+    P.obj_lrec = reinterpret_cast<const float4*>(c->p_obj_lrec);
+    P.box_obj = c->p_box_obj; P.sph_obj = c->p_sph_obj;
+    P.cold = c->p_cold; P.lights = c->p_lights; P.cams = c->d_cams.p;
     P.counters = c->d_cnt.p;
     P.tile_counter = c->d_tile.p;
     P.n_box = c->n_box; P.n_sph = c->n_sph; P.n_lights = c->n_lights; P.max_depth = c->max_depth;
@@ -518,7 +539,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         P.group_k = (P.packet && !(o.no_cull & 64)) ? group_k : 0.0f;
         P.group_cos = group_cos;
     }
-    P.extent = reinterpret_cast<const float*>(c->d_extent.p);
+    P.extent = reinterpret_cast<const float*>(c->p_extent);
     if (P.block) {
         // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
         P.blist_stride = c->n_box + c->n_sph;

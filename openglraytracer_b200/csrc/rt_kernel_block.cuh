@@ -123,9 +123,9 @@ __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, con
         if (SMEM) c = smem_f4[sph ? w.sph_off4 + (uint32_t)(hot - P.n_box) : w.box_off4 + (uint32_t)hot];
         else c = sph ? __ldg(P.sph_hot + (hot - P.n_box)) : __ldg(P.box_cull + hot);
         const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
-        // mode 0: every selected entry goes on; 1: the warp's cone and fan plane; 2: no cone (only near points);
+        // mode 1: the warp's cone and fan plane; 2: no cone (only near points);
         // ball_r > 0: plus the ball around the apex that holds the warp's near points
-        const bool pass = sel && (mode == 0 || (mode == 1 && cone_pass<true>(cone, c, rp)) ||
+        const bool pass = sel && ((mode == 1 && cone_pass<true>(cone, c, rp)) ||
                                   (ball_r > 0.0f && ball_pass(cone.apex, ball_r, c, rp)));
         if (COUNT) cnt.packet_tests += sel;
         unsigned mask = __ballot_sync(kFull, pass);
@@ -406,7 +406,6 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     if (lane == 0) { bs->mx[warp][4 * k] = s2w; bs->mx[warp][4 * k + 1] = lw; bs->mx[warp][4 * k + 2] = okw ? 1.0f : 0.0f; bs->mx[warp][4 * k + 3] = nw; bs->hw[warp][k] = hwp; }
                 }
                 __syncthreads();                                                    // maxima visible
-                bool b_ok = true;
                 float ball[kShadowBatch];
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
@@ -427,14 +426,14 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     ball[k] = nmax > 0.0f ? __fmaf_rn(sqrt_approx(nmax), 1.0001f, 0.0101f) : 0.0f;
                 }
                 const bool any_b = on != 0u || ball[0] > 0.0f || ball[1] > 0.0f || ball[2] > 0.0f;
-                // every thread holds the same `on`, `b_ok`, cones (all read from shared memory): CTA-uniform
-                if (b_ok && any_b)
+                // every thread holds the same `on`, balls and cones (all read from shared memory): CTA-uniform.  The list
+                // cannot overflow: one entry per object at most, and the CTA's slice holds n_hot entries.
+                if (any_b)
                     block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
                 __syncthreads();                                                    // list B complete
                 const int nb = (int)bs->count_b[s & 1];
                 if (threadIdx.x == 0) bs->count_b[(s + 1) & 1] = 0u;                // its readers (sample s - 1) are past two barriers
-                const bool use_b = b_ok && nb <= P.blist_stride;
-                if (logging) { log_nb = (unsigned)nb; log_flags |= (use_b ? 1u : 2u) | (on << 4) | (ball[0] > 0.0f ? 0x100u : 0u) | (ball[1] > 0.0f ? 0x200u : 0u) | (ball[2] > 0.0f ? 0x400u : 0u); }
+                if (logging) { log_nb = (unsigned)nb; log_flags |= 1u | (on << 4) | (ball[0] > 0.0f ? 0x100u : 0u) | (ball[1] > 0.0f ? 0x200u : 0u) | (ball[2] > 0.0f ? 0x400u : 0u); }
 
                 // ---- this warp's root shadow rays, light by light (one cone over its own 96 hit points)
                 if (packet) {
@@ -485,17 +484,11 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             const bool has_far = __any_sync(kFull, far_pt);
                             const float nw = warp_max_nonneg(nmax);
                             const float ball_r = nw > 0.0f ? __fmaf_rn(sqrt_approx(nw), 1.0001f, 0.0101f) : 0.0f;
-                            // without the block list the per-warp scan needs one narrow cone and nothing else
-                            if (!use_b && (!narrow || ball_r > 0.0f)) { have_sb = false; break; }
                             cone_close(wc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
-                            if (use_b) {
-                                if (!narrow) cone_open(wc[0]);                            // reach and fan plane only
-                                const float hwp = warp_max_nonneg(hmax < 1e30f ? hmax : 1e30f);
-                                cone_fan(wc[0], wn, P.fan ? hwp : 3e38f, pk_pad1);
-                            }
+                            if (!narrow) cone_open(wc[0]);                                // reach and fan plane only
+                            cone_fan(wc[0], wn, P.fan ? warp_max_nonneg(hmax < 1e30f ? hmax : 1e30f) : 3e38f, pk_pad1);
                             int unused[kShadowBatch] = {-1, -1, -1};
-                            if (use_b) list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, has_far ? 1 : 2, ball_r, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
-                            else packet_trace<SMEM, COUNT, 1>(P, w, wc, 1u, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
+                            list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, has_far ? 1 : 2, ball_r, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
                                 if (k == 0) rsb[q][0] = sbk[q]; else if (k == 1) rsb[q][1] = sbk[q]; else rsb[q][2] = sbk[q];

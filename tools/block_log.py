@@ -2,7 +2,7 @@
 
 RT_BLOCK_LOG=path makes the instrumented twin write one 16-word record per block:
   [0,1] start (globaltimer ns)  [2] ns until list A is complete  [3] list A entries  [4] list B entries
-  [5] flags: 1 use_b, 2 !use_b, 4 use_a, 8 !use_a, bits 4-6 light cones on, bits 8-10 balls
+  [5] flags: 1 list B used (always; 2 = not, older logs), 4 use_a, 8 !use_a, bits 4-6 light cones on, bits 8-10 balls
   [6] SM id  [7] CTA  [8..15] ns from block start until warp k reached the end of its work item
 Usage: python tools/block_log.py n_objects [width height depth]   |   python tools/block_log.py --analyze log.bin
 """
