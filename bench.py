@@ -60,6 +60,9 @@ BATCH_FRAMES = 256
 # `ncu --set full` captures (profiles/r1_ncu_full_*.txt); the 8.3 MB frame mostly stays in the 126 MB L2.
 NCU_DRAM_BYTES = {"builtin_1080p_d4": 58624 + 1224192, "scaled_1k_1080p_d0": 8672512 + 167796736,
                   "scaled_64k_1080p_d0": 11898368 + 177194752}
+# smsp__issue_active.avg.pct_of_peak_sustained_active of the timed kernel from the same captures: the share of issue
+# slots in use (an FP32-issue-bound kernel's real ceiling; `frac` counts algorithmic flops only)
+NCU_ISSUE_ACTIVE = {"builtin_1080p_d4": 0.830, "scaled_1k_1080p_d0": 0.451, "scaled_64k_1080p_d0": 0.526}
 DEFAULT_WORKLOAD = "builtin_1080p_d4"
 METRIC = "Mrays/s (rays x bounces)"
 UNIT = "Mrays/s"
@@ -399,10 +402,11 @@ def run_gpu(args, wl_name, wl):
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved / peak_tf, "traffic": NCU_DRAM_BYTES.get(wl_name),
+                         "issue_slots_active_ncu": NCU_ISSUE_ACTIVE.get(wl_name),
                          "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/); algorithmic bytes = the "
                                          "%d-byte frame + the scene records: FP32-issue bound, not HBM; the large-scene "
-                                         "kernels also write back their per-thread pending-ray stacks (1.4 KB x 75 776 "
-                                         "threads)" % (nfr * w * h * 4),
+                                         "kernels also write back the local-memory frames of their resident threads (1.8 KB x "
+                                         "75 776 threads) once per launch" % (nfr * w * h * 4),
                          "peak_source": "FP32 FMA-chain microbenchmark in this run (MEASURED_PEAKS.json has no FP32 "
                                         "figure); nominal 148 SM x 128 x 2 x 1.965 GHz = 74.4",
                          "algorithmic_flops_per_launch": flops_per_frame, "kernel_ms": kernel_ms,
