@@ -1081,7 +1081,10 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
                 }
             }
         }
-        if (!SMEM) asm volatile("cp.async.wait_group 0;" ::: "memory");   // nothing of this pass may land later
+        if (!SMEM) {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");          // nothing of this pass may land later:
+            __syncwarp();                                                 // the next user of the buffers may be a TMA tile
+        }
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) { best_io[r] = rs.best[r]; bidx_io[r] = rs.bidx[r]; }
