@@ -326,6 +326,25 @@ def test_bounding_sphere_test_far_and_tiny_objects(tracer):
             _check(on, ref, "far/tiny objects", need_edges=False)
 
 
+def test_block_log_records_every_block(tracer, tmp_path, monkeypatch):
+    """RT_BLOCK_LOG: the instrumented twin of the block kernel writes one 16-word record per block of 48 x 16
+    pixels (profiling aid); the frame is the same with the log on."""
+    sc, cam = rt.scaled_scene(300, max_depth=0), rt.builtin_camera(0.0)
+    w, h = 200, 70                                   # 5 x 5 blocks, ragged on both edges
+    plain = tracer.render(sc, cam, w, h)
+    path = tmp_path / "blocks.bin"
+    monkeypatch.setenv("RT_BLOCK_LOG", str(path))
+    img, st = tracer.render(sc, cam, w, h, want_stats=True)
+    monkeypatch.delenv("RT_BLOCK_LOG")
+    assert np.array_equal(img, plain)
+    rec = np.fromfile(path, dtype=np.uint32).reshape(-1, 16)
+    assert rec.shape[0] == 25
+    start = rec[:, 0].astype(np.uint64) | (rec[:, 1].astype(np.uint64) << np.uint64(32))
+    assert (start > 0).all() and (rec[:, 8:16].max(axis=1) > 0).all()       # every block ran, every record has times
+    assert (rec[:, 3] <= sc.objects_count).all() and (rec[:, 4] <= sc.objects_count).all()   # list sizes
+    assert (rec[:, 5] & 1).all()                                            # the shadow list was used
+
+
 def test_edge_case_scenes(tracer):
     cam = rt.builtin_camera(0.0)
     # empty scene: every ray misses -> black, alpha 0 (semantics item 7)
