@@ -58,7 +58,7 @@ WORKLOADS = {
 BATCH_FRAMES = 256
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the timed kernel, from the committed
 # `ncu --set full` captures (profiles/r1_ncu_full_*.txt); the 8.3 MB frame mostly stays in the 126 MB L2.
-NCU_DRAM_BYTES = {"builtin_1080p_d4": 58624 + 1224192, "scaled_1k_1080p_d0": 8672512 + 167796736,
+NCU_DRAM_BYTES = {"builtin_1080p_d4": 58368 + 1266688, "scaled_1k_1080p_d0": 8672512 + 167796736,
                   "scaled_64k_1080p_d0": 11898368 + 177194752}
 # smsp__issue_active.avg.pct_of_peak_sustained_active of the timed kernel from the same captures: the share of issue
 # slots in use (an FP32-issue-bound kernel's real ceiling; `frac` counts algorithmic flops only)
