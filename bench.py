@@ -236,7 +236,10 @@ def run_gpu(args, wl_name, wl):
         raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_cpus = None
     if world > 1:
+        from openglraytracer_b200.multigpu import bind_to_gpu_numa
+        numa_cpus = bind_to_gpu_numa(local)         # before any page-locked allocation
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
@@ -395,6 +398,7 @@ def run_gpu(args, wl_name, wl):
                                    "cannot change the pixel are counted but not traversed",
                        "frames_per_step": BATCH_FRAMES if batch else world,
                        "parallelism": "frames sharded over %d GPU(s), no data-path collective" % world,
+                       "host_binding": ("each rank on the %d cores next to its GPU (NVML affinity)" % len(numa_cpus)) if numa_cpus else "launcher default",
                        "l2": "flushed between timed steps (256 MiB write)", "kernel": "fast (fmad on, no fast-math)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": scene_bytes,
                     "d2h_bytes_per_step": nfr * w * h * 4, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,

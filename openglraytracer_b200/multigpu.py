@@ -8,8 +8,31 @@ whole frames and needs no exchange at all.
 torch is plumbing only: device buffers, streams and torch.distributed (NCCL
 over NVLink on the GPU box, gloo in the CPU tests).
 """
+import os
+
 import torch
 import torch.distributed as dist
+
+
+def bind_to_gpu_numa(device_index):
+    """One process per GPU: run this process on the CPU cores next to its GPU (NVML's ideal CPU affinity), so
+    that the page-locked host frame the kernel stores into is allocated on the GPU's own NUMA node and the
+    posted PCIe writes do not cross sockets.  Returns the cores bound to, or None when NVML is not usable (the
+    process then stays where the launcher put it)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        n_cpu = os.cpu_count() or 1
+        handle = pynvml.nvmlDeviceGetHandleByIndex(int(device_index))
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (n_cpu + 63) // 64)
+        cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (int(wd) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:        # noqa: BLE001 - best effort: no NVML, no permission, unknown topology
+        return None
 
 
 def row_band(rank, world, height):

@@ -126,3 +126,13 @@ def test_feedback_refinement_converges_on_a_synthetic_cost():
         assert all(bands[i][1] == bands[i + 1][0] for i in range(g - 1))
     imbalance = max(times(bands)) / (true_cost.sum() / g)
     assert imbalance0 > 1.5 and imbalance < 1.05
+
+
+def test_numa_binding_is_best_effort():
+    """bind_to_gpu_numa: without a usable NVML (this container) it leaves the process where it is and says so."""
+    import os
+    from openglraytracer_b200.multigpu import bind_to_gpu_numa
+    before = os.sched_getaffinity(0)
+    got = bind_to_gpu_numa(0)
+    after = os.sched_getaffinity(0)
+    assert got is None and after == before or (got is not None and set(got) == after and after <= before)
