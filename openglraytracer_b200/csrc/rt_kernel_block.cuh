@@ -47,14 +47,6 @@ __device__ __forceinline__ unsigned smid() {
     return v;
 }
 
-// Rays that start within `radius` of the apex and run toward it stay inside that ball: the bounding sphere
-// (c, rp) can only matter if it reaches into the ball.
-__device__ __forceinline__ bool ball_pass(V3 apex, float radius, float4 c, float rp) {
-    const V3 v = mk(c.x - apex.x, c.y - apex.y, c.z - apex.z);
-    const float far = radius + rp;
-    return __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z))) <= __fmul_rn(far, far);
-}
-
 // All threads of the CTA: one object per thread and trip against NC cones; hits are appended to `list`.
 template <bool SMEM, bool COUNT, int NC>
 __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w, const Cone (&cone)[NC], unsigned on,
