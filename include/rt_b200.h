@@ -118,6 +118,8 @@ typedef struct rt_stats {
     uint64_t loop_passes;     /* bounce rays: passes made by the per-ray loops for what the groups left over (per warp) */
     uint64_t candidates;      /* objects that passed a packet test and went through the per-ray tests (per warp) */
     uint64_t shadow_group_passes;      /* bounce rays: passes made for a group of neighbouring hit points' shadow rays (per warp) */
+    uint64_t shaded_lights;   /* (hit node, light) pairs whose diffuse + specular terms were evaluated (glsl:822-833): the
+                                 unoccluded ones among the traversed shadow rays (shadow_rays - rays_not_traversed) */
 } rt_stats;
 
 /* Extended options; zero-initialise then override (rt_options_default()). The
@@ -132,7 +134,9 @@ typedef struct rt_options {
     int32_t device;           /* CUDA device ordinal; -1 = current device */
     int32_t strict;           /* 1 = strict-arithmetic kernel (-fmad=false, IEEE divides, shader op order) */
     int32_t async;            /* 1 = do not synchronise (device output only); pair with rt_synchronize() */
-    void* stream;             /* cudaStream_t to launch on; NULL = the context's own stream */
+    void* stream;             /* cudaStream_t to launch on; NULL = the context's own stream.  Scene uploads run on the
+                               * context's stream; a render on another stream is ordered after the last upload, and the
+                               * next upload after that render, by events (one caller stream at a time per context) */
     rt_stats* stats;          /* optional counters/timings */
     int32_t host_store;       /* page-locked host out_rgba: RT_HOST_STORE_AUTO (0) lets the kernel store the frame
                                * straight into it over PCIe when the frame is heavy enough to hide the traffic,
@@ -146,6 +150,11 @@ typedef struct rt_options {
                                * packets (per-ray loops) */
 } rt_options;
 
+/* Environment variables (read once per process; profiling / tuning aids, results are byte-identical whatever they
+ * say):  RT_GROUP_K    bounce rays as grouped packets: (group radius / scene extent)^2, default 0.01
+ *        RT_GROUP_COS  ... and the cosine of the largest angle between a group member and its leader, default 0.99
+ *        RT_BLOCK_LOG  path: the instrumented twin of the block kernel (rt_options.stats != NULL) dumps one 64-byte
+ *                      timing record per block of 48 x 16 pixels there (tools/block_log.py) */
 #define RT_HOST_STORE_AUTO   0
 #define RT_HOST_STORE_ALWAYS 1
 #define RT_HOST_STORE_NEVER  2

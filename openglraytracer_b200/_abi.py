@@ -54,7 +54,7 @@ class Stats(C.Structure):
                 ("red_pixels", C.c_uint64), ("rays_not_traversed", C.c_uint64), ("kernel_ms", C.c_float), ("total_ms", C.c_float),
                 ("cull_tests", C.c_uint64), ("warp_iters", C.c_uint64),
                 ("packet_tests", C.c_uint64), ("group_passes", C.c_uint64), ("loop_passes", C.c_uint64),
-                ("candidates", C.c_uint64), ("shadow_group_passes", C.c_uint64)]
+                ("candidates", C.c_uint64), ("shadow_group_passes", C.c_uint64), ("shaded_lights", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

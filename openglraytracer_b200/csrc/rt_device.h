@@ -83,6 +83,7 @@ struct RtCounters {
     unsigned long long loop_passes;  /* per warp (lane 0): per-ray loop passes for bounce rays the groups left over */
     unsigned long long candidates;   /* per warp (lane 0): candidate_test calls */
     unsigned long long shadow_group_passes;   /* per warp (lane 0): passes for the shadow rays of a group of hit points */
+    unsigned long long shaded_lights;  /* (hit node, light) pairs whose diffuse + specular terms were evaluated (glsl:822-833) */
 };
 
 struct RtParams {

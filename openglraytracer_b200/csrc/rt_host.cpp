@@ -118,6 +118,11 @@ struct rt_context {
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    // Ordering between the context's own stream (scene uploads, prologue kernels) and a caller's stream
+    // (rt_options.stream): a render on another stream waits for ev_upload; the next upload waits (on the host,
+    // it rewrites the page-locked staging block and the device arena) for ev_render of the last such render.
+    cudaEvent_t ev_upload = nullptr, ev_render = nullptr;
+    bool upload_recorded = false, render_recorded = false;
     DevBuf<float> d_box_fast, d_box_strict, d_box_cull, d_obj_lrec, d_sph;
     DevBuf<int32_t> d_box_obj, d_sph_obj;
     DevBuf<RtCold> d_cold;
@@ -294,6 +299,8 @@ int rt_create(rt_context** out_ctx, int device) {
     CU(rt_strict::configure(device, &c->max_smem_optin));
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) CU(cudaEventCreate(&c->ev[i]));
+    CU(cudaEventCreateWithFlags(&c->ev_upload, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->ev_render, cudaEventDisableTiming));
     CU(c->d_cnt.reserve(1));
     CU(c->d_tile.reserve(2));
     *out_ctx = c;
@@ -312,6 +319,9 @@ int rt_destroy(rt_context* c) {
     if (c->h_stage) cudaFreeHost(c->h_stage);
     c->d_arena.release();
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->render_recorded) cudaEventSynchronize(c->ev_render);
+    if (c->ev_upload) cudaEventDestroy(c->ev_upload);
+    if (c->ev_render) cudaEventDestroy(c->ev_render);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return RT_OK;
@@ -340,8 +350,9 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     int rc = build_host_scene(scene, &hs);
     if (rc != RT_OK) return rc;
     CU(cudaSetDevice(c->device));
-    // The previous frame may still be reading these buffers.
+    // The previous frame may still be reading these buffers -- on the context's stream or on a caller's.
     CU(cudaStreamSynchronize(c->stream));
+    if (c->render_recorded) CU(cudaEventSynchronize(c->ev_render));
     // layout of the arena: 256-byte aligned sections, 256 bytes of slack after each (pipelined record loads may read
     // a few records past the end of a list; what they read is never used)
     struct Sec { const void* src; size_t bytes; size_t off; };
@@ -362,6 +373,8 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     // the stream is idle (synchronised above), so the staging block of the previous upload has been consumed
     for (const Sec& x : sec) if (x.bytes) memcpy(c->h_stage + x.off, x.src, x.bytes);
     CU(cudaMemcpyAsync(c->d_arena.p, c->h_stage, total, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaEventRecord(c->ev_upload, c->stream));
+    c->upload_recorded = true;
     uint8_t* a = c->d_arena.p;
     c->p_extent = reinterpret_cast<const unsigned int*>(a + sec[0].off);
     c->p_box_fast = reinterpret_cast<const float*>(a + sec[1].off);
@@ -394,6 +407,7 @@ static int upload_device(rt_context* c, const rt_scene* scene) {
     const size_t nb = hs.box_obj.size(), ns = hs.sph_obj.size();
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
+    if (c->render_recorded) CU(cudaEventSynchronize(c->ev_render));
     CU(c->d_objs.reserve(n + 1));
     CU(c->d_kind.reserve(n + 1));
     CU(c->d_hot.reserve(n + 1));
@@ -421,6 +435,7 @@ static int upload_device(rt_context* c, const rt_scene* scene) {
                         c->d_extent.p, c->d_obj_lrec.p, c->stream));
     g_launches += 2 + (hs.n_lit > 0 ? 1 : 0);
     CU(cudaStreamSynchronize(c->stream));   // the host vectors above go out of scope
+    c->upload_recorded = false;             // complete: nothing for a caller's stream to wait for
     c->p_extent = c->d_extent.p; c->p_box_fast = c->d_box_fast.p; c->p_box_strict = nullptr; c->p_box_cull = c->d_box_cull.p;
     c->p_obj_lrec = c->d_obj_lrec.p; c->p_sph = c->d_sph.p; c->p_box_obj = c->d_box_obj.p; c->p_sph_obj = c->d_sph_obj.p;
     c->p_cold = c->d_cold.p; c->p_lights = c->d_lights.p;
@@ -484,6 +499,8 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         return fail(RT_ERR_BAD_ARG, "options.device %d != context device %d", o.device, c->device);
     CU(cudaSetDevice(c->device));
     cudaStream_t st = o.stream ? (cudaStream_t)o.stream : c->stream;
+    // a caller's stream is not ordered with the context's: the scene upload must have landed before this render reads it
+    if (st != c->stream && c->upload_recorded) CU(cudaStreamWaitEvent(st, c->ev_upload, 0));
 
     // camera prologue (glsl:366-383 hoisted)
     std::vector<RtCameraDev> cams(n_frames);
@@ -618,6 +635,10 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         }
     }
     if (o.stats) CU(cudaEventRecord(c->ev[3], st));
+    if (st != c->stream) {                  // the next upload must not overwrite what this render still reads
+        CU(cudaEventRecord(c->ev_render, st));
+        c->render_recorded = true;
+    }
     if (!o.async) {
         CU(cudaStreamSynchronize(st));   // glFinish() (main.cpp:238)
     }
@@ -632,6 +653,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         s->cull_tests = hc.cull_tests; s->warp_iters = hc.warp_iters; s->packet_tests = hc.packet_tests;
         s->group_passes = hc.group_passes; s->loop_passes = hc.loop_passes;
         s->candidates = hc.candidates; s->shadow_group_passes = hc.shadow_group_passes;
+        s->shaded_lights = hc.shaded_lights;
         CU(cudaEventElapsedTime(&s->kernel_ms, c->ev[0], c->ev[1]));
         CU(cudaEventElapsedTime(&s->total_ms, c->ev[2], c->ev[3]));
         if (blk_log_words) {

@@ -1423,33 +1423,56 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // One sample: recursive_raytrace (glsl:1071-1105) as a weighted pending-ray stack.
 // All 32 lanes run the loop together; a lane without work rides along inactive.
 // -------------------------------------------------------------------------
-template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
+// Pending rays of one lane: origin, direction, weight, remaining depth.  BOUNCE = false (MAX_RAYTRACE_DEPTH = 0,
+// the shader as shipped, glsl:22): the tree is its root, there is nothing to keep -- no local-memory frame at all.
+template <bool BOUNCE> struct RayStack;
+template <> struct RayStack<true> {
+    float stk[kStack][8];
+    int sp;
+    __device__ __forceinline__ void init(bool valid, V3 o, V3 d, int depth) { sp = 0; if (valid) push(o, d, 1.0f, depth); }
+    __device__ __forceinline__ bool pending() const { return sp > 0; }
+    __device__ __forceinline__ void clear() { sp = 0; }
+    __device__ __forceinline__ void push(V3 o, V3 d, float wgt, int depth) {
+        stk[sp][0] = o.x; stk[sp][1] = o.y; stk[sp][2] = o.z;
+        stk[sp][3] = d.x; stk[sp][4] = d.y; stk[sp][5] = d.z;
+        stk[sp][6] = wgt; stk[sp][7] = __int_as_float(depth);
+        ++sp;
+    }
+    __device__ __forceinline__ void pop(V3& o, V3& d, float& wgt, int& depth) {
+        --sp;
+        o = mk(stk[sp][0], stk[sp][1], stk[sp][2]);
+        d = mk(stk[sp][3], stk[sp][4], stk[sp][5]);
+        wgt = stk[sp][6]; depth = __float_as_int(stk[sp][7]);
+    }
+};
+template <> struct RayStack<false> {
+    V3 o0, d0;
+    bool live;
+    __device__ __forceinline__ void init(bool valid, V3 o, V3 d, int) { o0 = o; d0 = d; live = valid; }
+    __device__ __forceinline__ bool pending() const { return live; }
+    __device__ __forceinline__ void clear() { live = false; }
+    __device__ __forceinline__ void push(V3, V3, float, int) {}
+    __device__ __forceinline__ void pop(V3& o, V3& d, float& wgt, int& depth) { o = o0; d = d0; wgt = 1.0f; depth = 0; live = false; }
+};
+
+template <bool SMEM, bool REPACK, bool COUNT, bool CULL, bool BOUNCE = true>
 __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool valid, V3 org, V3 dir,
                                            bool have_first, float first_t, int first_idx, bool have_sb, const float (&first_sb)[kShadowBatch],
                                            float pk_pad1, float pk_pad2, RtCounters& cnt) {
-    // pending rays: origin, direction, weight, remaining depth
-    float stk[kStack][8];
-    int sp = 0;
-    if (valid) {
-        stk[0][0] = org.x; stk[0][1] = org.y; stk[0][2] = org.z;
-        stk[0][3] = dir.x; stk[0][4] = dir.y; stk[0][5] = dir.z;
-        stk[0][6] = 1.0f; stk[0][7] = __int_as_float(P.max_depth);
-        sp = 1;
-    }
+    RayStack<BOUNCE> stack;
+    stack.init(valid, org, dir, P.max_depth);
     V3 color = mk(0.0f, 0.0f, 0.0f);
     int iters = 0;   // loop iterations the shader's stack machine would have spent (glsl:1081-1094)
 
-    while (__any_sync(kFull, sp > 0)) {
-        const bool act = sp > 0;
+    while (__any_sync(kFull, stack.pending())) {
+        const bool act = stack.pending();
         V3 o[1], d[1];
         float wgt = 0.0f; int depth = 0;
         float best[1]; int bidx[1];
         bidx[0] = -1;
         if (act) {
-            --sp;
-            o[0] = mk(stk[sp][0], stk[sp][1], stk[sp][2]);
-            d[0] = mk(stk[sp][3], stk[sp][4], stk[sp][5]);
-            wgt = stk[sp][6]; depth = __float_as_int(stk[sp][7]);
+            stack.pop(o[0], d[0], wgt, depth);
+            if (!BOUNCE) depth = 0;
             best[0] = kFar;
         } else {
             o[0] = mk(0.0f, 0.0f, 0.0f); d[0] = mk(0.0f, 0.0f, 1.0f);
@@ -1496,8 +1519,8 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
         bool reflected = false, refracted = false;
         if (hit) {
             kr = mat->reflectivity; kt = mat->transparency;
-            reflected = depth > 0 && kr > 0.0f;
-            refracted = depth > 0 && kt > 0.0f;
+            reflected = BOUNCE && depth > 0 && kr > 0.0f;
+            refracted = BOUNCE && depth > 0 && kt > 0.0f;
             wp = wgt; wr = wgt * kr;
             if (reflected) wp = wp * (1.0f - kr);
             if (refracted) { wp = wp * (1.0f - kt); wr = wr * (1.0f - kt); }
@@ -1626,6 +1649,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 #pragma unroll
                 for (int r = 0; r < kShadowBatch; ++r) {
                     if (shade && r < n_slots && !(sb[r] < 1.0f)) {
+                        if (COUNT) cnt.shaded_lights++;
                         const RtLightDev* __restrict__ L = P.lights + li[r];
                         const V3 light_dir = normalize3(sd[r]);                                  // glsl:804
                         const V3 light_ref = normalize3(reflect3(-light_dir, h.n));              // glsl:825
@@ -1654,23 +1678,15 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                 // glsl:1013-1020: ratio = 1 / ior, inverted again when leaving the object; both IEEE
                 // quotients are per-object constants, built by the prologue
                 const float ratio = h.inside ? mat->ior_back : mat->inv_ior;
-                const V3 rdv = refract3(d[0], h.n, ratio);
-                stk[sp][0] = ro.x; stk[sp][1] = ro.y; stk[sp][2] = ro.z;
-                stk[sp][3] = rdv.x; stk[sp][4] = rdv.y; stk[sp][5] = rdv.z;
-                stk[sp][6] = wgt * kt; stk[sp][7] = __int_as_float(depth - 1);
-                ++sp;
+                stack.push(ro, refract3(d[0], h.n, ratio), wgt * kt, depth - 1);
             }
             if (reflected) {                                                                        // glsl:988-994
                 const V3 ro = axpy3(h.n, 0.001f, h.p);
-                const V3 rdv = reflect3(d[0], h.n);
-                stk[sp][0] = ro.x; stk[sp][1] = ro.y; stk[sp][2] = ro.z;
-                stk[sp][3] = rdv.x; stk[sp][4] = rdv.y; stk[sp][5] = rdv.z;
-                stk[sp][6] = wr; stk[sp][7] = __int_as_float(depth - 1);
-                ++sp;
+                stack.push(ro, reflect3(d[0], h.n), wr, depth - 1);
             }
         }
         // Runaway guard (glsl:1076-1101): red iff the stack machine needs >= 10001 iterations.
-        if (iters >= 10001) sp = 0;
+        if (iters >= 10001) stack.clear();
     }
     if (iters >= 10001) { if (COUNT) cnt.red_pixels++; return mk(1.0f, 0.0f, 0.0f); }
     return color;
@@ -1680,7 +1696,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 // The kernel.  grid = persistent CTAs; each warp walks 8x4-pixel tiles of all
 // frames (tile index -> frame, tile row, tile column).
 // -------------------------------------------------------------------------
-template <bool SMEM, bool REPACK, bool COUNT, bool CULL>
+template <bool SMEM, bool REPACK, bool COUNT, bool CULL, bool BOUNCE = true>
 __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL : RT_MIN_BLOCKS) : RT_MIN_BLOCKS_SMALL) render_kernel(const __grid_constant__ RtParams P) {
     // dynamic shared memory: [hot scene (resident only)] [per-warp scratch] [per-warp tile buffers + barriers (streaming only)]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1746,7 +1762,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     RtCounters cnt;
     cnt.packet_tests = cnt.group_passes = cnt.loop_passes = cnt.candidates = cnt.shadow_group_passes = 0ull;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
-    cnt.cull_tests = cnt.warp_iters = 0ull;
+    cnt.cull_tests = cnt.warp_iters = cnt.shaded_lights = 0ull;
 
     // Work distribution: the first round of tiles is static (tile = global warp id); after that
     // each warp pulls the next tile index from a global counter (zeroed by the host before the
@@ -1783,7 +1799,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
             }
             const float no_sb[kShadowBatch] = {0.0f, 0.0f, 0.0f};
             if (NP == 1) {
-                sum[0] = sum[0] + trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, valid[0], org, dir[0], false, 0.0f, -1, false, no_sb, 0.0f, 0.0f, cnt);
+                sum[0] = sum[0] + trace_sample<SMEM, REPACK, COUNT, CULL, BOUNCE>(P, w, valid[0], org, dir[0], false, 0.0f, -1, false, no_sb, 0.0f, 0.0f, cnt);
             } else {
                 // PHASE 0 of the three root frames (glsl:956-967), shared origin
                 V3 o3[kShadowBatch];
@@ -1919,7 +1935,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                     float fsb[kShadowBatch];
 #pragma unroll
                     for (int k = 0; k < kShadowBatch; ++k) fsb[k] = q == 0 ? rsb[0][k] : (q == 1 ? rsb[1][k] : rsb[2][k]);
-                    const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, have_sb, fsb, pk_pad1, pk_pad2, cnt);
+                    const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL, BOUNCE>(P, w, vq, org, dq, true, tq, iq, have_sb, fsb, pk_pad1, pk_pad2, cnt);
                     if (q == 0) sum[0] = sum[0] + c;
                     else if (q == 1) sum[1] = sum[1] + c;
                     else sum[2] = sum[2] + c;
@@ -1955,11 +1971,11 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
     if (COUNT) {
         // warp-reduce then one atomic per warp per counter
         if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
-        unsigned long long v[15] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+        unsigned long long v[16] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
                                     cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes,
-                                    cnt.candidates, cnt.shadow_group_passes};
+                                    cnt.candidates, cnt.shadow_group_passes, cnt.shaded_lights};
 #pragma unroll
-        for (int k = 0; k < 15; ++k) {
+        for (int k = 0; k < 16; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

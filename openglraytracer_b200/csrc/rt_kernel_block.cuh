@@ -134,7 +134,7 @@ __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, con
     for (int r = 0; r < kShadowBatch; ++r) { best_io[r] = rs.best[r]; bidx_io[r] = rs.bidx[r]; }
 }
 
-template <bool SMEM, bool COUNT>
+template <bool SMEM, bool COUNT, bool BOUNCE>
 __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_kernel(const __grid_constant__ RtParams P) {
     constexpr bool CULL = true, REPACK = true;
     constexpr int NP = kShadowBatch;
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
     RtCounters cnt;
     cnt.packet_tests = cnt.group_passes = cnt.loop_passes = cnt.candidates = cnt.shadow_group_passes = 0ull;
     cnt.rays = cnt.nodes = cnt.hit_nodes = cnt.shadow_rays = cnt.box_tests = cnt.sphere_tests = cnt.red_pixels = cnt.pad = 0ull;
-    cnt.cull_tests = cnt.warp_iters = 0ull;
+    cnt.cull_tests = cnt.warp_iters = cnt.shaded_lights = 0ull;
 
     for (long long blk = blockIdx.x; blk < n_blocks;) {
         // RT_BLOCK_LOG (instrumented twin only): when this block started, how long each warp worked, list sizes
@@ -499,7 +499,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 float fsb[kShadowBatch];
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) fsb[k] = q == 0 ? rsb[0][k] : (q == 1 ? rsb[1][k] : rsb[2][k]);
-                const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL>(P, w, vq, org, dq, true, tq, iq, have_sb, fsb, pk_pad1, pk_pad2, cnt);
+                const V3 c = trace_sample<SMEM, REPACK, COUNT, CULL, BOUNCE>(P, w, vq, org, dq, true, tq, iq, have_sb, fsb, pk_pad1, pk_pad2, cnt);
                 if (q == 0) sum[0] = sum[0] + c;
                 else if (q == 1) sum[1] = sum[1] + c;
                 else sum[2] = sum[2] + c;
@@ -545,11 +545,11 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
 
     if (COUNT) {
         if (lane != 0) cnt.warp_iters = 0ull;    // a per-warp count, kept by lane 0
-        unsigned long long v[15] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
+        unsigned long long v[16] = {cnt.rays, cnt.nodes, cnt.hit_nodes, cnt.shadow_rays, cnt.box_tests, cnt.sphere_tests,
                                     cnt.red_pixels, cnt.pad, cnt.cull_tests, cnt.warp_iters, cnt.packet_tests, cnt.group_passes, cnt.loop_passes,
-                                    cnt.candidates, cnt.shadow_group_passes};
+                                    cnt.candidates, cnt.shadow_group_passes, cnt.shaded_lights};
 #pragma unroll
-        for (int k = 0; k < 15; ++k) {
+        for (int k = 0; k < 16; ++k) {
             unsigned long long x = v[k];
             for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(kFull, x, off);
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);

@@ -87,7 +87,9 @@ def test_ragged_sizes(tracer, w, h):
     for strict in (True, False):
         img = tracer.render(sc, cam, w, h, strict=strict)
         rep = compare(img, ob.render(sc, cam, w, h))
-        assert rep["over_1"] <= max(1, int(0.02 * w * h)), rep
+        # below 1000 pixels the 99.9 % criterion cannot be met by a frame with one flipped silhouette pixel:
+        # one pixel beyond 1 LSB is allowed, no more
+        assert rep["over_1"] <= 1, rep
 
 
 def test_time_sweep_strict(tracer):
@@ -174,7 +176,7 @@ def test_scaled_scene_streaming_pixel_subset(tracer, n):
     sc, cam = rt.scaled_scene(n, max_depth=0), rt.builtin_camera(0.0)
     w, h = 1920, 1080
     rng = np.random.default_rng(0x5CE7E001)
-    npix = 4096 if n <= 16384 else 1024
+    npix = 4096
     pix = np.stack([rng.integers(0, w, npix), rng.integers(0, h, npix)], axis=1).astype(np.int32)
     ref = ob.render(sc, cam, w, h, pixels=pix)
     # render only the rows we need in chunks to keep the GPU time small: full frame is the product path
@@ -382,7 +384,10 @@ def test_runaway_guard_red_pixels_match(tracer):
     assert ost["red_pixels"] > 0
     red_ref = (ref[..., 0] == 255) & (ref[..., 1] == 0) & (ref[..., 2] == 0)
     red_gpu = (img[..., 0] == 255) & (img[..., 1] == 0) & (img[..., 2] == 0)
-    assert (red_ref != red_gpu).sum() <= 2 and abs(int(st["red_pixels"]) - int(ost["red_pixels"])) <= 2
+    # The strict kernel takes its matrices from the host prologue and follows the shader op for op (IEEE sqrt /
+    # divide, no FMA), so every hit decision -- and with it the size of every bounce tree -- is the oracle's:
+    # the red pixels are the same pixels, exactly.  (powf and the product weights only touch colours.)
+    assert (red_ref != red_gpu).sum() == 0 and int(st["red_pixels"]) == int(ost["red_pixels"])
 
 
 def test_bad_arguments_are_rejected(tracer):
@@ -401,7 +406,7 @@ def test_full_size_properties_1080p_and_4k(tracer):
     suite; use size-independent properties: determinism, band union == frame,
     alpha == 0, oracle agreement on a seeded pixel subset."""
     sc, cam = rt.builtin_scene(0.0, 4), rt.builtin_camera(0.0)
-    for (w, h, spp) in [(1920, 1080, 1), (3840, 2160, 4)]:
+    for (w, h, spp) in [(1920, 1080, 1), (3840, 2160, 16)]:        # BASELINE configs 2 and 3
         a = tracer.render(sc, cam, w, h, spp=spp)
         b = tracer.render(sc, cam, w, h, spp=spp)
         assert np.array_equal(a, b) and a[..., 3].max() == 0
@@ -411,7 +416,8 @@ def test_full_size_properties_1080p_and_4k(tracer):
             canvas[y0:y1] = tracer.render(sc, cam, w, h, spp=spp, y0=y0, y1=y1, band_only=True)
         assert np.array_equal(canvas, a)
         rng = np.random.default_rng(w)
-        pix = np.stack([rng.integers(0, w, 4096), rng.integers(0, h, 4096)], axis=1).astype(np.int32)
+        npix = 4096 if spp == 1 else 2048                          # 16 samples per pixel on the CPU
+        pix = np.stack([rng.integers(0, w, npix), rng.integers(0, h, npix)], axis=1).astype(np.int32)
         ref = ob.render(sc, cam, w, h, spp=spp, pixels=pix)
         assert_parity(a[pix[:, 1], pix[:, 0]], ref, "%dx%d subset" % (w, h))
 
@@ -420,3 +426,138 @@ def test_kernels_actually_launch(tracer):
     before = rt.kernel_launch_count()
     tracer.render(rt.builtin_scene(), rt.builtin_camera(), 64, 36)
     assert rt.kernel_launch_count() == before + 1
+
+
+# ---------------------------------------------------------------------------------------------
+# Exact ties (glsl:773): `if (c.t < closest)` with objects visited in index order -> on a bit-equal t the
+# LOWER original index wins.  The per-ray loops visit boxes then spheres in index order; the packet / block
+# kernels meet candidates in any order and apply the index rule explicitly (candidate_test).
+# ---------------------------------------------------------------------------------------------
+def _tie_scene(n_fill, order, kind):
+    """The scaled scene's first n_fill objects + two COINCIDENT objects (same geometry, different materials)
+    near the camera's line of sight; `order` swaps which material comes first."""
+    base = rt.scaled_scene(max(n_fill, 8), max_depth=1)
+    blt = rt.builtin_scene(0.0, 1)
+    n = n_fill + 2
+    objs = (rt.Object * n)()
+    for i in range(n_fill):
+        objs[i] = base.objects[i]
+    mats = [blt.objects[1].material, blt.objects[3].material]         # mirror, blue glass
+    for k in range(2):
+        o = objs[n_fill + k]
+        o.position[:] = [4.0, 2.0, 0.25]
+        o.angles[:] = [20.0, 35.0, 50.0]
+        o.sphere_radius = -1.0
+        if kind == "box":
+            o.box_mins[:] = [-1.5, -1.0, -1.25]
+            o.box_maxs[:] = [1.5, 1.0, 1.25]
+        else:
+            o.sphere_radius = 1.75
+        o.material = mats[k if order == 0 else 1 - k]
+    return rt.SceneData(objs, base.lights, 1)
+
+
+@pytest.mark.parametrize("kind", ["box", "sphere"])
+@pytest.mark.parametrize("n_fill", [3, 60, 130])
+def test_exact_tie_lower_index_wins(tracer, kind, n_fill):
+    cam = rt.builtin_camera(0.0)
+    w, h = 192, 108
+    frames = []
+    for order in (0, 1):
+        sc = _tie_scene(n_fill, order, kind)
+        ref = ob.render(sc, cam, w, h)
+        # the oracle itself: the pair is visible and the first of the two owns every pixel of it
+        first = ob.render(rt.SceneData((rt.Object * (n_fill + 1))(*list(sc.objects)[:n_fill + 1]), sc.lights, 1), cam, w, h)
+        assert np.array_equal(ref, first), "oracle: the second of two coincident objects must never win (glsl:773)"
+        modes = [0] if n_fill < 48 else ([0, 1, 4] if n_fill < 96 else [0, 1, 4, 8, 16, 16 | 32, 64, 8 | 64])
+        fast0 = None
+        for mode in modes:
+            img = tracer.render(sc, cam, w, h, no_cull=mode)
+            _check(img, ref, "tie %s n=%d order=%d no_cull=%d" % (kind, n_fill, order, mode), need_edges=False)
+            if fast0 is None:
+                fast0 = img
+            assert np.array_equal(img, fast0), mode              # every kernel family picks the same winner
+        _check(tracer.render(sc, cam, w, h, strict=True), ref, "tie strict", need_edges=False)
+        frames.append(fast0)
+    # the two orders differ where the pair is visible (different material in front): the test does test something
+    assert (frames[0] != frames[1]).any(axis=2).mean() > 0.01
+
+
+@pytest.mark.parametrize("n,depth", [(1024, 2), (16384, 2)])
+def test_scaled_depth2_1080p_pixel_subset(tracer, n, depth):
+    """The bench workloads scaled_1k_1080p_d2 / scaled_16k_1080p_d2 at full size: bounce rays as grouped packets
+    (secondary_packets), block kernel (1k) and per-warp kernel (16k), against the oracle on a seeded subset."""
+    sc, cam = rt.scaled_scene(n, max_depth=depth), rt.builtin_camera(0.0)
+    w, h = 1920, 1080
+    rng = np.random.default_rng(n + depth)
+    pix = np.stack([rng.integers(0, w, 4096), rng.integers(0, h, 4096)], axis=1).astype(np.int32)
+    ref = ob.render(sc, cam, w, h, pixels=pix)
+    img = tracer.render(sc, cam, w, h)
+    assert_parity(img[pix[:, 1], pix[:, 0]], ref, "scaled n=%d d=%d 1080p subset" % (n, depth))
+    assert int(img[..., 3].max()) == 0
+
+
+def test_batch256_turntable_pose_vs_oracle(tracer):
+    """BASELINE config 5: 256 turntable poses at 1024 x 1024, depth 4, one rt_render_batch call; poses out of the
+    batch against the oracle (seeded subset) and against the single-frame call (byte-identical)."""
+    import torch
+    sc = rt.builtin_scene(0.0, 4)
+    cams = rt.turntable_cameras(256)
+    w = h = 1024
+    dev = torch.empty((256, h, w, 4), dtype=torch.uint8, device="cuda:0")
+    torch.cuda.synchronize()
+    tracer.render(sc, cams, w, h, out_device_ptr=dev.data_ptr())
+    rng = np.random.default_rng(256)
+    pix = np.stack([rng.integers(0, w, 4096), rng.integers(0, h, 4096)], axis=1).astype(np.int32)
+    for k in (0, 77, 201):
+        frame = dev[k].cpu().numpy()
+        assert np.array_equal(frame, tracer.render(sc, cams[k], w, h))
+        ref = ob.render(sc, cams[k], w, h, pixels=pix)
+        assert_parity(frame[pix[:, 1], pix[:, 0]], ref, "batch pose %d" % k)
+    del dev
+
+
+def test_scene_upload_is_ordered_with_a_caller_stream(tracer):
+    """rt_options.stream: uploads run on the context's stream, the render on the caller's.  A time sweep that
+    re-uploads the (animated) scene before every asynchronous render on a caller stream must give the frames of
+    the synchronous path -- the render waits for the upload, the next upload waits for the render."""
+    import torch
+    w, h = 256, 144
+    times = [0.25 * k for k in range(12)]
+    want = [tracer.render(rt.builtin_scene(t, 3), rt.builtin_camera(t), w, h) for t in times]
+    stream = torch.cuda.Stream("cuda:0")
+    outs = [torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0") for _ in times]
+    big = torch.empty(64 << 20, dtype=torch.uint8, device="cuda:0")
+    torch.cuda.synchronize()
+    for rounds in range(3):
+        for t, out in zip(times, outs):
+            with torch.cuda.stream(stream):
+                big.zero_()                                     # keeps the caller's stream busy ahead of the render
+            tracer.render(rt.builtin_scene(t, 3), rt.builtin_camera(t), w, h, out_device_ptr=out.data_ptr(),
+                          async_=True, stream=stream.cuda_stream)
+        stream.synchronize()
+        for t, out, ref in zip(times, outs, want):
+            assert np.array_equal(out.cpu().numpy(), ref), "t=%g round %d" % (t, rounds)
+    # large scene through the device prologue, same pattern
+    sc = rt.scaled_scene(2048)
+    ref = tracer.render(sc, rt.builtin_camera(0.0), w, h)
+    for _ in range(3):
+        with torch.cuda.stream(stream):
+            big.zero_()
+        tracer.render(sc, rt.builtin_camera(0.0), w, h, out_device_ptr=outs[0].data_ptr(), async_=True,
+                      stream=stream.cuda_stream)
+        tracer.render(rt.builtin_scene(0.0, 0), rt.builtin_camera(0.0), w, h, out_device_ptr=outs[1].data_ptr(),
+                      async_=True, stream=stream.cuda_stream)
+        stream.synchronize()
+        assert np.array_equal(outs[0].cpu().numpy(), ref)
+
+
+def test_shaded_light_counter(tracer):
+    """rt_stats.shaded_lights: (hit node, light) pairs actually shaded = traversed shadow rays that were not occluded;
+    bench.py credits the 95-flop Phong term per shaded light only."""
+    sc, cam = rt.builtin_scene(0.0, 2), rt.builtin_camera(0.0)
+    _, st = tracer.render(sc, cam, 320, 180, want_stats=True)
+    traversed = st["shadow_rays"] - st["rays_not_traversed"]
+    assert 0 < st["shaded_lights"] < traversed <= st["shadow_rays"]
+    _, ost = ob.render(sc, cam, 320, 180, want_stats=True)
+    assert st["shadow_rays"] == ost["shadow_rays"]
