@@ -148,6 +148,10 @@ typedef struct rt_options {
                                * also below RT_BLOCK_MIN_OBJECTS objects (test switch); bit 5 = shadow packets without
                                * their fan planes (cone and reach only); bit 6 = bounce rays are not grouped into
                                * packets (per-ray loops) */
+    void* done_flag;          /* optional device pointer to a 32-bit completion word -- typically in ANOTHER GPU's memory,
+                               * mapped with rt_ipc_import: the launch's last CTA stores done_value there (system-scope
+                               * release) once every framebuffer store of the call is visible; pair with rt_wait_flags() */
+    uint32_t done_value;
 } rt_options;
 
 /* Environment variables (read once per process; profiling / tuning aids, results are byte-identical whatever they
@@ -264,6 +268,17 @@ int rt_device_free(void* device_ptr);
 int rt_ipc_export(void* device_ptr, uint8_t handle64[64]);
 int rt_ipc_import(const uint8_t handle64[64], void** device_ptr);
 int rt_ipc_close(void* device_ptr);
+
+/* Consumer side of rt_options.done_flag (multi-GPU frame mode without a collective): one warp on `stream` waits
+ * until each of the n words at flags_dev (device memory of the current device) has reached `value` (epochs only
+ * grow; wrap-safe).  Work queued on the stream behind it sees every byte the producers stored before raising
+ * their word.  Gives up after timeout_ms (<= 0: 2000) so that a lost producer cannot hang the GPU;
+ * rt_wait_flags_status() then returns 1. */
+int rt_wait_flags(const uint32_t* flags_dev, int n, uint32_t value, int timeout_ms, void* stream);
+int rt_wait_flags_status(void);
+/* Raises a 32-bit word to `value` in stream order (system-scope release) -- the word may be read by other GPUs
+ * that mapped the allocation ("frame consumed": producers wait for it before they overwrite the frame). */
+int rt_write_flag(uint32_t* flag_dev, uint32_t value, void* stream);
 
 #ifdef __cplusplus
 }

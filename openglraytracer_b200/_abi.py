@@ -64,7 +64,8 @@ class Options(C.Structure):
     _fields_ = [("spp", C.c_int32), ("seed", C.c_uint32), ("y0", C.c_int32), ("y1", C.c_int32),
                 ("out_is_device", C.c_int32), ("out_band_only", C.c_int32), ("device", C.c_int32),
                 ("strict", C.c_int32), ("async_", C.c_int32), ("stream", C.c_void_p),
-                ("stats", C.POINTER(Stats)), ("host_store", C.c_int32), ("no_cull", C.c_int32)]
+                ("stats", C.POINTER(Stats)), ("host_store", C.c_int32), ("no_cull", C.c_int32),
+                ("done_flag", C.c_void_p), ("done_value", C.c_uint32)]
 
 
 # Every symbol include/rt_b200.h declares (tests check the library exports all of them).
@@ -74,7 +75,7 @@ EXPORTS = [
     "rt_render_batch", "rt_upload_scene", "rt_render_uploaded", "rt_builtin_scene", "rt_builtin_camera",
     "rt_orbit_camera", "rt_scaled_scene", "rt_write_ppm", "rt_write_raw", "rt_fp32_peak_tflops",
     "rt_ipc_export", "rt_ipc_import", "rt_ipc_close", "rt_device_alloc", "rt_device_free",
-    "rt_set_prologue", "rt_scene_save", "rt_scene_load", "rt_scene_file_scene", "rt_scene_file_camera", "rt_scene_file_free",
+    "rt_wait_flags", "rt_wait_flags_status", "rt_write_flag", "rt_set_prologue", "rt_scene_save", "rt_scene_load", "rt_scene_file_scene", "rt_scene_file_camera", "rt_scene_file_free",
 ]
 
 _lib = None
@@ -120,6 +121,9 @@ def lib():
     L.rt_device_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     L.rt_device_free.argtypes = [vp]
     L.rt_set_prologue.argtypes = [vp, C.c_int]
+    L.rt_wait_flags.argtypes = [vp, C.c_int, C.c_uint32, C.c_int, vp]
+    L.rt_wait_flags_status.argtypes = []
+    L.rt_write_flag.argtypes = [vp, C.c_uint32, vp]
     L.rt_scene_save.argtypes = [C.c_char_p, C.POINTER(Scene), C.POINTER(Camera)]
     L.rt_scene_load.argtypes = [C.c_char_p, C.POINTER(vp)]
     L.rt_scene_file_scene.argtypes = [vp]

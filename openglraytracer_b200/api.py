@@ -163,7 +163,8 @@ class Raytracer:
         check(self._lib.rt_synchronize(self._ctx), "rt_synchronize")
 
     @staticmethod
-    def _options(spp, seed, y0, y1, strict, out_is_device, band_only, async_, stream, stats, no_cull=False, host_store=0):
+    def _options(spp, seed, y0, y1, strict, out_is_device, band_only, async_, stream, stats, no_cull=False, host_store=0,
+                 done_flag=None, done_value=0):
         o = Options()
         _abi.lib().rt_options_default(C.byref(o))
         o.spp, o.seed, o.y0, o.y1 = int(spp), int(seed), int(y0), int(y1)
@@ -172,6 +173,9 @@ class Raytracer:
         o.stream = stream
         o.no_cull = int(no_cull)
         o.host_store = int(host_store)
+        if done_flag:
+            o.done_flag = C.c_void_p(int(done_flag))
+            o.done_value = int(done_value) & 0xFFFFFFFF
         if stats is not None:
             o.stats = C.pointer(stats)
         return o
@@ -183,12 +187,14 @@ class Raytracer:
 
     def render(self, scene, camera_uniforms, width, height, *, spp=1, seed=0x5EED0001, y0=0, y1=0,
                strict=False, out=None, out_device_ptr=None, band_only=False, async_=False, stream=None,
-               want_stats=False, no_cull=False, host_store=0):
+               want_stats=False, no_cull=False, host_store=0, done_flag=None, done_value=0):
         """Render one frame (camera_uniforms: Camera) or a batch (ctypes array of Camera).
 
         scene=None re-uses the last uploaded scene.  Host output: numpy uint8
         [H, W, 4] (or [n, H, W, 4]); with band_only the H axis is y1-y0.  Device
         output: pass out_device_ptr (e.g. torch_tensor.data_ptr()), returns None.
+        done_flag / done_value (device output only): rt_options.done_flag, the completion word the launch's
+        last CTA writes (multi-GPU frame mode, see multigpu.PeerFrame).
         """
         batch = isinstance(camera_uniforms, C.Array)
         n = len(camera_uniforms) if batch else 1
@@ -198,7 +204,8 @@ class Raytracer:
         rows = (yy1 - max(y0, 0)) if band_only else height
         stats = Stats() if want_stats else None
         if out_device_ptr is not None:
-            opts = self._options(spp, seed, y0, y1, strict, 1, band_only, async_, stream, stats, no_cull)
+            opts = self._options(spp, seed, y0, y1, strict, 1, band_only, async_, stream, stats, no_cull,
+                                 done_flag=done_flag, done_value=done_value)
             target = C.c_void_p(int(out_device_ptr))
             result = None
         else:
@@ -224,6 +231,16 @@ def fp32_peak_tflops(device=-1, iters=4096):
     ms = C.c_float()
     check(_abi.lib().rt_fp32_peak_tflops(device, iters, C.byref(tf), C.byref(ms)), "rt_fp32_peak_tflops")
     return tf.value, ms.value
+
+
+def wait_flags(flags_device_ptr, n, value, stream=None, timeout_ms=2000):
+    """One warp on `stream` waits until the n 32-bit words at flags_device_ptr have reached `value` (rt_wait_flags)."""
+    check(_abi.lib().rt_wait_flags(C.c_void_p(int(flags_device_ptr)), int(n), int(value) & 0xFFFFFFFF, int(timeout_ms),
+                                   C.c_void_p(stream) if stream else None), "rt_wait_flags")
+
+
+def wait_flags_timed_out():
+    return _abi.lib().rt_wait_flags_status() == 1
 
 
 def kernel_launch_count():

@@ -557,6 +557,8 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         P.group_cos = group_cos;
     }
     P.extent = reinterpret_cast<const float*>(c->p_extent);
+    P.done_flag = reinterpret_cast<uint32_t*>(o.done_flag);
+    P.done_value = o.done_value;
     if (P.block) {
         // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
         P.blist_stride = c->n_box + c->n_sph;

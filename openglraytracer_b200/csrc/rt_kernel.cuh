@@ -1693,6 +1693,27 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
 }
 
 // -------------------------------------------------------------------------
+// Completion flag (rt_options.done_flag): the last CTA of the launch writes P.done_value to a 32-bit word --
+// usually in ANOTHER GPU's memory (multi-GPU frame mode: the word sits next to rank 0's frame, mapped through CUDA
+// IPC) -- once every framebuffer store of the launch is visible system-wide.  The consumer's stream waits for the
+// word (rt_wait_flags) instead of for a collective.  Order: each thread's stores, fence.sys, CTA barrier, one
+// device-scope atomic per CTA on the launch's finished-CTA counter; the CTA that sees gridDim.x - 1 is the last
+// one: fence.sys (cumulative over what the counter carried), then a system-scope release store of the value.
+// -------------------------------------------------------------------------
+__device__ __forceinline__ void signal_done(const RtParams& P) {
+    if (P.done_flag == nullptr) return;                       // grid-uniform
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned long long prev = atomicAdd(P.tile_counter + 1, 1ull);
+        if (prev == (unsigned long long)gridDim.x - 1ull) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.done_flag), "r"(P.done_value) : "memory");
+        }
+    }
+}
+
+// -------------------------------------------------------------------------
 // The kernel.  grid = persistent CTAs; each warp walks 8x4-pixel tiles of all
 // frames (tile index -> frame, tile row, tile column).
 // -------------------------------------------------------------------------
@@ -1981,6 +2002,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);
         }
     }
+    signal_done(P);
 }
 
 #if !RT_STRICT

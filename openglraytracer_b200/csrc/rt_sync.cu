@@ -1,0 +1,75 @@
+// Device-side completion of the multi-GPU frame mode: the consumer side of rt_options.done_flag.
+//
+// Every rank's render kernel stores its row band straight into rank 0's frame over NVLink and its last CTA
+// writes the frame's epoch to that rank's word of a flag array next to the frame (rt_kernel.cuh: signal_done).
+// rt_wait_flags puts ONE warp on the consumer's stream that spins (system-scope acquire loads) until every word
+// has reached the epoch: what is ordered behind it on that stream sees the whole frame.  No collective, no host
+// round trip -- a 4-byte NCCL all-reduce used as completion flag was 40 % of a 0.17 ms frame at 8 GPUs.
+//
+// A producer that never arrives must not hang the device: the wait gives up after timeout_ms and raises the
+// status word, which rt_wait_flags_status reads back.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/rt_b200.h"
+
+namespace {
+__global__ void wait_flags_kernel(const uint32_t* flags, int n, uint32_t value, unsigned long long timeout_ns,
+                                  uint32_t* status) {
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    bool late = false;
+    for (int i = threadIdx.x; i < n; i += 32) {
+        for (;;) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
+            if ((int32_t)(v - value) >= 0) break;           // epochs only grow (wrap-safe compare)
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > timeout_ns) { late = true; break; }
+            __nanosleep(64);
+        }
+    }
+    if (late) atomicExch(status, 1u);
+    __threadfence_system();
+}
+uint32_t* g_status[64] = {nullptr};
+}  // namespace
+
+extern "C" int rt_wait_flags(const uint32_t* flags_dev, int n, uint32_t value, int timeout_ms, void* stream) {
+    if (!flags_dev || n <= 0) return RT_ERR_BAD_ARG;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return RT_ERR_NO_DEVICE;
+    if (dev < 0 || dev >= 64) return RT_ERR_BAD_ARG;
+    if (!g_status[dev]) {
+        if (cudaMalloc((void**)&g_status[dev], sizeof(uint32_t)) != cudaSuccess) return RT_ERR_CUDA;
+        if (cudaMemset(g_status[dev], 0, sizeof(uint32_t)) != cudaSuccess) return RT_ERR_CUDA;
+    }
+    const unsigned long long ns = (unsigned long long)(timeout_ms > 0 ? timeout_ms : 2000) * 1000000ull;
+    wait_flags_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(flags_dev, n, value, ns, g_status[dev]);
+    return cudaGetLastError() == cudaSuccess ? RT_OK : RT_ERR_CUDA;
+}
+
+// 0 = every wait so far was satisfied, 1 = some wait timed out (synchronises the device)
+extern "C" int rt_wait_flags_status(void) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return RT_ERR_NO_DEVICE;
+    if (dev < 0 || dev >= 64 || !g_status[dev]) return 0;
+    uint32_t v = 0;
+    if (cudaMemcpy(&v, g_status[dev], sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return RT_ERR_CUDA;
+    return (int)v;
+}
+
+namespace {
+__global__ void write_flag_kernel(uint32_t* flag, uint32_t value) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+}  // namespace
+
+// Raises a 32-bit word to `value` in stream order (system-scope release): the "frame consumed" word of the
+// multi-GPU frame mode, which the producers' streams wait for before their kernels may overwrite the frame.
+extern "C" int rt_write_flag(uint32_t* flag_dev, uint32_t value, void* stream) {
+    if (!flag_dev) return RT_ERR_BAD_ARG;
+    write_flag_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag_dev, value);
+    return cudaGetLastError() == cudaSuccess ? RT_OK : RT_ERR_CUDA;
+}

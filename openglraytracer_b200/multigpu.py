@@ -110,48 +110,58 @@ def frame_stride_set(rank, world, n_frames):
     return list(range(rank, n_frames, world))
 
 
-def gather_bands(band, height, width, group=None, dst=0, bands=None):
+def gather_bands(band, height, width, group=None, dst=0, bands=None, out=None):
     """Gather every rank's band (uint8 [rows_r, W, 4]) into the full frame on `dst`.
 
-    Bands may differ in height (H % G != 0, or cost-balanced bands); they are padded to the
-    largest band for the collective and trimmed on arrival.  Returns uint8 [H, W, 4] on dst, None
-    elsewhere.
+    One grouped exchange of point-to-point operations of the EXACT band sizes: every other rank sends its
+    band, `dst` receives each one straight into its rows of the frame (`out`: a persistent uint8 [H, W, 4]
+    tensor, allocated when missing).  No padding to the tallest band, no staging copies after the
+    collective (NCCL 2.27 has no ncclGather; a dist.gather of padded bands plus eight slice copies was
+    slower at 8 GPUs than at 4).  Returns the frame on dst, None elsewhere.
     """
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     if bands is None:
         bands = [row_band(r, world, height) for r in range(world)]
-    max_rows = max(b - a for a, b in bands)
     y0, y1 = bands[rank]
     assert band.shape == (y1 - y0, width, 4) and band.dtype == torch.uint8, (band.shape, band.dtype)
-    if y1 - y0 == max_rows:
-        send = band.contiguous()
-    else:
-        send = torch.zeros((max_rows, width, 4), dtype=torch.uint8, device=band.device)
-        send[: y1 - y0] = band
+
+    def peer(r):        # P2POp wants global ranks
+        return dist.get_global_rank(group, r) if group is not None else r
+
     if rank == dst:
-        parts = [torch.empty_like(send) for _ in range(world)]
-        dist.gather(send, parts, dst=dst, group=group)
-        frame = torch.empty((height, width, 4), dtype=torch.uint8, device=band.device)
-        for r in range(world):
-            a, b = bands[r]
-            frame[a:b] = parts[r][: b - a]
-        return frame
-    dist.gather(send, None, dst=dst, group=group)
-    return None
+        frame = out if out is not None else torch.empty((height, width, 4), dtype=torch.uint8, device=band.device)
+        mine = frame[y0:y1]
+        if mine.data_ptr() != band.data_ptr():
+            mine.copy_(band)
+        ops = [dist.P2POp(dist.irecv, frame[bands[r][0]:bands[r][1]], peer(r), group)
+               for r in range(world) if r != dst and bands[r][1] > bands[r][0]]
+    else:
+        frame = None
+        ops = [dist.P2POp(dist.isend, band.contiguous(), peer(dst), group)] if y1 > y0 else []
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return frame
 
 
 class BandRenderer:
     """Row-band renderer of one rank: renders rows [y0, y1) of every frame into a
-    device tensor through the C ABI (device output, caller's stream)."""
+    device tensor through the C ABI (device output, caller's stream).  On rank `dst` the band IS the
+    rank's slice of a persistent full frame, so its own rows need no copy."""
 
-    def __init__(self, raytracer, width, height, rank, world, device, bands=None):
+    def __init__(self, raytracer, width, height, rank, world, device, bands=None, dst=0):
         self.rt = raytracer
         self.width, self.height = width, height
-        self.rank, self.world = rank, world
+        self.rank, self.world, self.dst = rank, world, dst
         self.bands = bands if bands is not None else [row_band(r, world, height) for r in range(world)]
         self.y0, self.y1 = self.bands[rank]
-        self.band = torch.empty((self.y1 - self.y0, width, 4), dtype=torch.uint8, device=device)
+        self.frame = None
+        if rank == dst:
+            self.frame = torch.empty((height, width, 4), dtype=torch.uint8, device=device)
+            self.band = self.frame[self.y0:self.y1]
+        else:
+            self.band = torch.empty((self.y1 - self.y0, width, 4), dtype=torch.uint8, device=device)
         # A real stream handle: the C ABI reads a NULL stream as "the context's own stream",
         # and torch's legacy default stream IS the NULL handle.
         self.stream = torch.cuda.Stream(device)
@@ -168,7 +178,8 @@ class BandRenderer:
     def render_and_gather(self, scene, camera, group=None, **kw):
         band = self.render(scene, camera, **kw)
         with torch.cuda.stream(self.stream):
-            frame = gather_bands(band, self.height, self.width, group=group, bands=self.bands)
+            frame = gather_bands(band, self.height, self.width, group=group, dst=self.dst, bands=self.bands,
+                                 out=self.frame)
         torch.cuda.current_stream(self.band.device).wait_stream(self.stream)
         return frame
 
@@ -176,16 +187,23 @@ class BandRenderer:
 class _RawCudaBuffer:
     """A cudaMalloc'ed buffer exposed through __cuda_array_interface__ so that torch can view it."""
 
-    def __init__(self, ptr, shape):
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (int(ptr), False),
+    def __init__(self, ptr, shape, typestr="|u1"):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
                                          "version": 2, "strides": None}
 
 
 class PeerFrame:
     """Fused gather (SURVEY §5 / §8e stage 2): rank `dst` owns the frame; every other rank maps
     it through a CUDA IPC handle and its render kernel's 16-byte framebuffer stores
-    (rt_kernel.cuh, glsl:404 imageStore) land directly in that buffer over NVLink.  The only
-    collective left is a one-element all-reduce that tells `dst` every band is complete."""
+    (rt_kernel.cuh, glsl:404 imageStore) land directly in that buffer over NVLink.
+
+    No collective on the frame's path at all.  Behind the frame sit world + 1 32-bit words in the same
+    allocation: word r is raised to the frame's epoch by the LAST CTA of rank r's kernel once all its stores
+    are visible system-wide (rt_options.done_flag; rt_kernel.cuh signal_done), and `dst` puts one warp on its
+    stream that waits for all of them (rt_wait_flags).  The last word runs the other way: `dst` raises it to
+    k - 1 when the caller asks for frame k (the previous frame is then his to overwrite), and every producer's
+    stream waits for it before its kernel may store -- so a fast rank never writes into a frame `dst` still
+    reads.  Setup (IPC handle exchange) uses torch.distributed once; frames do not."""
 
     def __init__(self, raytracer, width, height, rank, world, device, group=None, dst=0, bands=None):
         import ctypes as C
@@ -197,20 +215,25 @@ class PeerFrame:
         self.stream = torch.cuda.Stream(device)
         self._lib = _abi.lib()
         nbytes = width * height * 4
+        self._flags_off = (nbytes + 255) // 256 * 256
+        total = self._flags_off + 4 * (world + 1) + 256
         handle = torch.zeros(64, dtype=torch.uint8, device=device)
         self._own = C.c_void_p()
         self._mapped = C.c_void_p()
+        self.epoch = 0
         # Every rank goes through the same collectives whatever fails locally; the outcome is agreed
         # with an all-reduce so that either all ranks own a working PeerFrame or all raise.
         err = None
         self.ptr = None
         if rank == dst:
             try:
-                _abi.check(self._lib.rt_device_alloc(C.byref(self._own), nbytes), "rt_device_alloc")
+                _abi.check(self._lib.rt_device_alloc(C.byref(self._own), total), "rt_device_alloc")
                 buf = C.create_string_buffer(64)
                 _abi.check(self._lib.rt_ipc_export(self._own, buf), "rt_ipc_export")
                 handle.copy_(torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8))
                 self.ptr = self._own.value
+                torch.as_tensor(_RawCudaBuffer(self.ptr + self._flags_off, (4 * (world + 1),)), device=device).zero_()
+                torch.cuda.synchronize(device)
             except Exception as exc:
                 err = exc
         dist.broadcast(handle, src=dst, group=group)
@@ -232,18 +255,28 @@ class PeerFrame:
         self.frame = None
         if rank == dst:
             self.frame = torch.as_tensor(_RawCudaBuffer(self.ptr, (height, width, 4)), device=device)
-        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self._flags = self.ptr + self._flags_off              # word r: rank r's band of the current epoch is complete
+        self._consumed = self._flags + 4 * world              # raised by dst: frames up to this epoch may be overwritten
 
     def render(self, scene, camera, **kw):
-        """All ranks: render this rank's band into dst's frame, then the completion all-reduce.
-        Returns the full frame (uint8 [H, W, 4]) on dst, None elsewhere; ordered on the caller's
-        current stream."""
+        """All ranks: render this rank's band of the next frame into dst's frame.  Returns the full frame (uint8
+        [H, W, 4]) on dst -- valid for work queued on the caller's current stream, until the next render() call,
+        which hands it back to the producers -- and None elsewhere.  No host synchronisation, no collective."""
+        from . import api
         cur = torch.cuda.current_stream(self.device)
         self.stream.wait_stream(cur)
+        self.epoch += 1
+        st = self.stream.cuda_stream
+        if self.rank == self.dst:
+            # whatever the caller queued on `cur` that reads the previous frame is ordered before this
+            _check(self._lib.rt_write_flag(self._consumed, (self.epoch - 1) & 0xFFFFFFFF, st), "rt_write_flag")
+        else:
+            api.wait_flags(self._consumed, 1, self.epoch - 1, stream=st)
         self.rt.render(scene, camera, self.width, self.height, y0=self.y0, y1=self.y1, band_only=False,
-                       out_device_ptr=self.ptr, async_=True, stream=self.stream.cuda_stream, **kw)
-        with torch.cuda.stream(self.stream):
-            dist.all_reduce(self._flag, group=self.group)
+                       out_device_ptr=self.ptr, async_=True, stream=st,
+                       done_flag=self._flags + 4 * self.rank, done_value=self.epoch, **kw)
+        if self.rank == self.dst:
+            api.wait_flags(self._flags, self.world, self.epoch, stream=st)
         cur.wait_stream(self.stream)
         return self.frame
 
@@ -270,9 +303,26 @@ class PeerFrame:
             mine = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float32, device=self.device)
             every = [torch.zeros_like(mine) for _ in range(self.world)]
             dist.all_gather(every, mine, group=self.group)
-            bands = refine_row_bands(bands, [float(t.item()) for t in every], self.height)
+            self.band_ms = [float(t.item()) for t in every]
+            bands = refine_row_bands(bands, self.band_ms, self.height)
         self.set_bands(bands)
         return bands
+
+    def measure_bands(self, scene, camera, **kw):
+        """Per-band kernel time (ms) of the current bands, one entry per rank (a tiny all-gather)."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))
+        for k in range(2):
+            if k == 1:
+                e0.record(self.stream)
+            self.rt.render(scene, camera, self.width, self.height, y0=self.y0, y1=self.y1, band_only=False,
+                           out_device_ptr=self.ptr, async_=True, stream=self.stream.cuda_stream, **kw)
+        e1.record(self.stream)
+        self.stream.synchronize()
+        mine = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float32, device=self.device)
+        every = [torch.zeros_like(mine) for _ in range(self.world)]
+        dist.all_gather(every, mine, group=self.group)
+        return [float(t.item()) for t in every]
 
     def close(self):
         torch.cuda.synchronize(self.device)
@@ -285,3 +335,8 @@ class PeerFrame:
             self.frame = None
             self._lib.rt_device_free(self._own)
             self._own = None
+
+
+def _check(code, where):
+    from . import _abi
+    _abi.check(code, where)

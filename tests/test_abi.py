@@ -49,14 +49,16 @@ def test_ctypes_mirrors_match_the_header(tmp_path):
     from openglraytracer_b200 import _abi
     src = tmp_path / "sizes.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "rt_b200.h"\n'
-                   'int main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(rt_stats), sizeof(rt_options), '
+                   'int main(void) { printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(rt_stats), sizeof(rt_options), '
                    'sizeof(rt_object), sizeof(rt_light), sizeof(rt_camera), sizeof(rt_material), '
-                   'offsetof(rt_stats, shadow_group_passes), offsetof(rt_options, no_cull)); return 0; }\n')
+                   'offsetof(rt_stats, shadow_group_passes), offsetof(rt_options, no_cull), offsetof(rt_stats, shaded_lights), '
+                   'offsetof(rt_options, done_value)); return 0; }\n')
     exe = tmp_path / "sizes"
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
     want = [C.sizeof(_abi.Stats), C.sizeof(_abi.Options), C.sizeof(rt.Object), C.sizeof(rt.Light), C.sizeof(rt.Camera),
-            C.sizeof(rt.Material), _abi.Stats.shadow_group_passes.offset, _abi.Options.no_cull.offset]
+            C.sizeof(rt.Material), _abi.Stats.shadow_group_passes.offset, _abi.Options.no_cull.offset,
+            _abi.Stats.shaded_lights.offset, _abi.Options.done_value.offset]
     assert got == want
 
 

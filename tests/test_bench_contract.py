@@ -46,3 +46,54 @@ def test_product_arm_has_no_cpu_fallback():
     r = _run(["--steps", "1", "--warmup", "0"])
     assert r.returncode != 0
     assert "no CUDA device" in (r.stderr + r.stdout) and "no CPU fallback" in (r.stderr + r.stdout)
+
+
+def test_reference_arm_uses_all_host_threads_under_torchrun():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU arm must still use every host
+    thread (round 1's N > 1 reference lines ran on one thread) and describe the workload with the very dict the
+    GPU arm prints, whatever --gpus says."""
+    sys.path.insert(0, ROOT)
+    import bench
+    r = _run(["--impl", "reference", "--steps", "1", "--warmup", "0", "--gpus", "2", "--workload", "builtin_720p_d0"],
+             env={"RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0", "OMP_NUM_THREADS": "1"})
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert d["config"] == bench.static_config("builtin_720p_d0", bench.WORKLOADS["builtin_720p_d0"], 2)
+    if len(os.sched_getaffinity(0)) > 1:
+        one = _run(["--impl", "reference", "--steps", "1", "--warmup", "0", "--workload", "builtin_720p_d0"])
+        v1 = json.loads([l for l in one.stdout.splitlines() if l.startswith("{")][0])["value"]
+        assert d["value"] > 0.5 * v1            # not a one-thread run: same ball park as the plain launch
+
+
+def test_roofline_flops_credit_executed_work_only():
+    """bench.algorithmic_flops: 95 flop per SHADED light (not per shadow ray the reference would cast), 5 per
+    traversed shadow ray, nothing for untraversed ones."""
+    sys.path.insert(0, ROOT)
+    import bench
+    st = dict(box_tests=0, sphere_tests=0, cull_tests=0, packet_tests=0, hit_nodes=0, shaded_lights=0,
+              shadow_rays=300, rays_not_traversed=100)
+    assert bench.algorithmic_flops(st, 0) == 5.0 * 200
+    st["shaded_lights"] = 120
+    assert bench.algorithmic_flops(st, 0) == 5.0 * 200 + 95.0 * 120
+    st["rays_not_traversed"] = 300
+    st["shaded_lights"] = 0
+    assert bench.algorithmic_flops(st, 10) == 76.0 * 10
+
+
+def test_ncu_figures_are_tied_to_the_kernel_sources(tmp_path, monkeypatch):
+    sys.path.insert(0, ROOT)
+    import bench
+    sha = bench.csrc_sha()
+    prof = tmp_path / "profiles"
+    prof.mkdir()
+    monkeypatch.setattr(bench, "ROOT", str(tmp_path))
+    monkeypatch.setattr(bench, "csrc_sha", lambda: sha)
+    assert bench.ncu_capture("builtin_1080p_d4")[0] is None
+    ent = {"csrc_sha": sha, "file": "profiles/x.txt", "dram_bytes_read": 10, "dram_bytes_write": 5, "issue_active": 0.8}
+    (prof / "ncu_captures.json").write_text(json.dumps({"kernels": {"builtin_1080p_d4": ent}}))
+    assert bench.ncu_capture("builtin_1080p_d4")[:2] == (15, 0.8)
+    ent["csrc_sha"] = "0" * 16
+    (prof / "ncu_captures.json").write_text(json.dumps({"kernels": {"builtin_1080p_d4": ent}}))
+    t, i, why = bench.ncu_capture("builtin_1080p_d4")
+    assert t is None and i is None and "stale" in why

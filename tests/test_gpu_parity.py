@@ -561,3 +561,38 @@ def test_shaded_light_counter(tracer):
     assert 0 < st["shaded_lights"] < traversed <= st["shadow_rays"]
     _, ost = ob.render(sc, cam, 320, 180, want_stats=True)
     assert st["shadow_rays"] == ost["shadow_rays"]
+
+
+def test_completion_flag_and_wait(tracer):
+    """rt_options.done_flag / rt_wait_flags / rt_write_flag on one GPU: the launch's last CTA raises the word to the
+    epoch after all framebuffer stores; a wait queued behind it passes; a wait for an epoch nobody raises gives up
+    after its timeout instead of hanging the device (multi-GPU frame mode, multigpu.PeerFrame)."""
+    import torch
+    from openglraytracer_b200 import api
+    w, h = 320, 180
+    stream = torch.cuda.Stream("cuda:0")
+    flags = torch.zeros(4, dtype=torch.int32, device="cuda:0")
+    out = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda:0")
+    torch.cuda.synchronize()
+    for sc in (rt.builtin_scene(0.0, 2), rt.builtin_scene(0.0, 0), rt.scaled_scene(300), rt.scaled_scene(60, max_depth=1)):
+        ref = tracer.render(sc, rt.builtin_camera(0.0), w, h)
+        for epoch in (1, 2, 3):
+            out.zero_()
+            torch.cuda.synchronize()
+            tracer.render(None, rt.builtin_camera(0.0), w, h, out_device_ptr=out.data_ptr(), async_=True,
+                          stream=stream.cuda_stream, done_flag=flags.data_ptr() + 4, done_value=epoch)
+            api.wait_flags(flags.data_ptr() + 4, 1, epoch, stream=stream.cuda_stream)
+            stream.synchronize()
+            assert int(flags[1].item()) == epoch and int(flags[0].item()) == 0
+            assert np.array_equal(out.cpu().numpy(), ref)
+        flags.zero_()
+        torch.cuda.synchronize()
+    assert not api.wait_flags_timed_out()
+    from openglraytracer_b200 import _abi
+    _abi.check(_abi.lib().rt_write_flag(flags.data_ptr() + 8, 7, stream.cuda_stream), "rt_write_flag")
+    api.wait_flags(flags.data_ptr() + 8, 1, 7, stream=stream.cuda_stream)
+    stream.synchronize()
+    assert int(flags[2].item()) == 7 and not api.wait_flags_timed_out()
+    api.wait_flags(flags.data_ptr() + 12, 1, 5, stream=stream.cuda_stream, timeout_ms=50)     # nobody raises word 3
+    stream.synchronize()
+    assert api.wait_flags_timed_out()
