@@ -273,7 +273,7 @@ int rt_ipc_close(void* device_ptr);
  * until each of the n words at flags_dev (device memory of the current device) has reached `value` (epochs only
  * grow; wrap-safe).  Work queued on the stream behind it sees every byte the producers stored before raising
  * their word.  Gives up after timeout_ms (<= 0: 2000) so that a lost producer cannot hang the GPU;
- * rt_wait_flags_status() then returns 1. */
+ * rt_wait_flags_status() then returns 1 (once: reading clears it). */
 int rt_wait_flags(const uint32_t* flags_dev, int n, uint32_t value, int timeout_ms, void* stream);
 int rt_wait_flags_status(void);
 /* Raises a 32-bit word to `value` in stream order (system-scope release) -- the word may be read by other GPUs

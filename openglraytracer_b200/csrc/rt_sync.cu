@@ -49,13 +49,14 @@ extern "C" int rt_wait_flags(const uint32_t* flags_dev, int n, uint32_t value, i
     return cudaGetLastError() == cudaSuccess ? RT_OK : RT_ERR_CUDA;
 }
 
-// 0 = every wait so far was satisfied, 1 = some wait timed out (synchronises the device)
+// 0 = every wait since the last call was satisfied, 1 = some wait timed out (synchronises the device; clears the word)
 extern "C" int rt_wait_flags_status(void) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return RT_ERR_NO_DEVICE;
     if (dev < 0 || dev >= 64 || !g_status[dev]) return 0;
     uint32_t v = 0;
     if (cudaMemcpy(&v, g_status[dev], sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return RT_ERR_CUDA;
+    if (v && cudaMemset(g_status[dev], 0, sizeof(uint32_t)) != cudaSuccess) return RT_ERR_CUDA;
     return (int)v;
 }
 
