@@ -498,8 +498,8 @@ def run_gpu(args, wl_name, wl):
                 timed_out = rt.api.wait_flags_timed_out()
                 pf.close()
                 out[label] = {"ms_per_frame": ms_p,
-                              "collective": "none: kernels store into rank 0's frame over NVLink (CUDA IPC mapping); the last "
-                                            "CTA of each rank's kernel raises a completion word there, one warp on rank 0 waits",
+                              "collective": "none: kernels store into rank 0's frame over NVLink (CUDA IPC mapping); a one-thread "
+                                            "kernel behind each rank's render raises a completion word there, one warp on rank 0 waits",
                               "bands": str(bset), "band_kernel_ms": band_ms,
                               "imbalance_max_over_mean": max(band_ms) / (sum(band_ms) / len(band_ms)),
                               "completion_and_launch_ms": ms_p - max(band_ms),

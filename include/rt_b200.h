@@ -149,8 +149,9 @@ typedef struct rt_options {
                                * their fan planes (cone and reach only); bit 6 = bounce rays are not grouped into
                                * packets (per-ray loops) */
     void* done_flag;          /* optional device pointer to a 32-bit completion word -- typically in ANOTHER GPU's memory,
-                               * mapped with rt_ipc_import: the launch's last CTA stores done_value there (system-scope
-                               * release) once every framebuffer store of the call is visible; pair with rt_wait_flags() */
+                               * mapped with rt_ipc_import: done_value is stored there (system-scope release, a one-thread
+                               * kernel in stream order behind the render) once every framebuffer store of the call is
+                               * visible; pair with rt_wait_flags() */
     uint32_t done_value;
 } rt_options;
 

@@ -98,7 +98,7 @@ struct RtParams {
     const RtCameraDev* cams;
     uint8_t* out;               /* frame k at out + k*frame_stride */
     RtCounters* counters;       /* used by the instrumented twin only */
-    unsigned long long* tile_counter;  /* [0] dynamic tile scheduler, [1] finished CTAs (completion flag); zeroed before each launch */
+    unsigned long long* tile_counter;  /* dynamic tile scheduler, zeroed before each launch */
     long long frame_stride;     /* bytes */
     int32_t n_box, n_sph, n_lights, max_depth;
     int32_t n_frames, width, height, y0, y1;
@@ -121,8 +121,6 @@ struct RtParams {
     float group_cos;            /* bounce rays join a group when their direction is within this cosine of the leader's */
     float group_k;              /* > 0: secondary rays are traced as grouped packets; group radius^2 = E^2 * group_k */
     uint32_t* blk_log;          /* block kernel, instrumented twin only (RT_BLOCK_LOG=path): 16 words per block, see tools/block_log.py */
-    uint32_t* done_flag;        /* completion word (may live in a peer GPU's memory), written by the launch's last CTA; NULL = none */
-    uint32_t done_value;
 };
 
 #endif

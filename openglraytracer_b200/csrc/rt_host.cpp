@@ -557,8 +557,6 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         P.group_cos = group_cos;
     }
     P.extent = reinterpret_cast<const float*>(c->p_extent);
-    P.done_flag = reinterpret_cast<uint32_t*>(o.done_flag);
-    P.done_value = o.done_value;
     if (P.block) {
         // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
         P.blist_stride = c->n_box + c->n_sph;
@@ -627,6 +625,15 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         g_launches++;
     }
 
+    // Completion word (multi-GPU frame mode): raised in stream order behind the render kernel -- at a kernel
+    // boundary every framebuffer store of the launch is visible, the one-thread kernel then stores the value with
+    // system-scope release.  (Written by the render kernel's own last CTA it cost the small-scene kernel 4 % more
+    // instructions and 6 % of its time: the epilogue upset the register allocation of the whole kernel.)
+    if (o.done_flag) {
+        if (rt_write_flag(reinterpret_cast<uint32_t*>(o.done_flag), o.done_value, st) != RT_OK)
+            return fail(RT_ERR_CUDA, "completion-flag launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        g_launches++;
+    }
     if (!o.out_is_device && !host_mapped) {
         uint8_t* dst = (uint8_t*)out_rgba;
         for (int k = 0; k < n_frames; k++) {

@@ -1352,6 +1352,8 @@ __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const WarpCtx& w, 
     int face = 0;                                                   // glsl:699-704
     if (t == by) face = 1;
     else if (t == bz) face = 2;
+    const float* m = c->nmat;                                       // glsl:718, column-major
+#if RT_STRICT
     // ray in the box's (unscaled) local space, as the shader computes it (glsl:655-656)
     const float* m4 = c->w2l;
     V3 rs, rd;
@@ -1360,13 +1362,25 @@ __device__ __forceinline__ Hit resolve_hit(const RtParams& P, const WarpCtx& w, 
     const float rdf = face == 0 ? rd.x : (face == 1 ? rd.y : rd.z);
     V3 nl = mk(face == 0 ? 1.0f : 0.0f, face == 1 ? 1.0f : 0.0f, face == 2 ? 1.0f : 0.0f);   // glsl:707-708
     if (rdf > 0.0f) nl = nl * -1.0f;                                // glsl:712-715
-    const float* m = c->nmat;                                       // glsl:718, column-major
     h.n.x = madd(m[6], nl.z, madd(m[3], nl.y, __fmul_rn(m[0], nl.x)));
     h.n.y = madd(m[7], nl.z, madd(m[4], nl.y, __fmul_rn(m[1], nl.x)));
     h.n.z = madd(m[8], nl.z, madd(m[5], nl.y, __fmul_rn(m[2], nl.x)));
     const V3 ql = axpy3(rd, t, rs);                                 // glsl:721
     const float* l = c->l2w;
     h.p = mk(row_pt(l, ql), row_pt(l + 4, ql), row_pt(l + 8, ql));
+#else
+    // Shipped kernel: the same quantities without the detour through the box's local space.
+    //  * normal = +-column `face` of the normal matrix (glsl:707-718: the matrix times a signed unit vector);
+    //    the sign is the sign of the local direction component (glsl:712), which the unit-frame direction
+    //    `ld` of the slab test shares (its rows are the local rows scaled by 1 / half-extent > 0);
+    //  * hit point = o + t d, which is what local_to_world * (ray_start + t * ray_dir) (glsl:721) equals before
+    //    rounding (ulp-level difference, stated in DESIGN.md 7).
+    const float ldf = face == 0 ? ld.x : (face == 1 ? ld.y : ld.z);
+    const float sg = ldf > 0.0f ? -1.0f : 1.0f;
+    const float* mc = m + 3 * face;
+    h.n = mk(__fmul_rn(mc[0], sg), __fmul_rn(mc[1], sg), __fmul_rn(mc[2], sg));
+    h.p = axpy3(d, t, o);
+#endif
     return h;
 }
 
@@ -1427,22 +1441,22 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // the shader as shipped, glsl:22): the tree is its root, there is nothing to keep -- no local-memory frame at all.
 template <bool BOUNCE> struct RayStack;
 template <> struct RayStack<true> {
-    float stk[kStack][8];
+    float4 stk[kStack][2];          // two 16-byte local-memory accesses per push / pop
     int sp;
     __device__ __forceinline__ void init(bool valid, V3 o, V3 d, int depth) { sp = 0; if (valid) push(o, d, 1.0f, depth); }
     __device__ __forceinline__ bool pending() const { return sp > 0; }
     __device__ __forceinline__ void clear() { sp = 0; }
     __device__ __forceinline__ void push(V3 o, V3 d, float wgt, int depth) {
-        stk[sp][0] = o.x; stk[sp][1] = o.y; stk[sp][2] = o.z;
-        stk[sp][3] = d.x; stk[sp][4] = d.y; stk[sp][5] = d.z;
-        stk[sp][6] = wgt; stk[sp][7] = __int_as_float(depth);
+        stk[sp][0] = make_float4(o.x, o.y, o.z, d.x);
+        stk[sp][1] = make_float4(d.y, d.z, wgt, __int_as_float(depth));
         ++sp;
     }
     __device__ __forceinline__ void pop(V3& o, V3& d, float& wgt, int& depth) {
         --sp;
-        o = mk(stk[sp][0], stk[sp][1], stk[sp][2]);
-        d = mk(stk[sp][3], stk[sp][4], stk[sp][5]);
-        wgt = stk[sp][6]; depth = __float_as_int(stk[sp][7]);
+        const float4 a = stk[sp][0], b = stk[sp][1];
+        o = mk(a.x, a.y, a.z);
+        d = mk(a.w, b.x, b.y);
+        wgt = b.z; depth = __float_as_int(b.w);
     }
 };
 template <> struct RayStack<false> {
@@ -1690,27 +1704,6 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
     }
     if (iters >= 10001) { if (COUNT) cnt.red_pixels++; return mk(1.0f, 0.0f, 0.0f); }
     return color;
-}
-
-// -------------------------------------------------------------------------
-// Completion flag (rt_options.done_flag): the last CTA of the launch writes P.done_value to a 32-bit word --
-// usually in ANOTHER GPU's memory (multi-GPU frame mode: the word sits next to rank 0's frame, mapped through CUDA
-// IPC) -- once every framebuffer store of the launch is visible system-wide.  The consumer's stream waits for the
-// word (rt_wait_flags) instead of for a collective.  Order: each thread's stores, fence.sys, CTA barrier, one
-// device-scope atomic per CTA on the launch's finished-CTA counter; the CTA that sees gridDim.x - 1 is the last
-// one: fence.sys (cumulative over what the counter carried), then a system-scope release store of the value.
-// -------------------------------------------------------------------------
-__device__ __forceinline__ void signal_done(const RtParams& P) {
-    if (P.done_flag == nullptr) return;                       // grid-uniform
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned long long prev = atomicAdd(P.tile_counter + 1, 1ull);
-        if (prev == (unsigned long long)gridDim.x - 1ull) {
-            __threadfence_system();
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.done_flag), "r"(P.done_value) : "memory");
-        }
-    }
 }
 
 // -------------------------------------------------------------------------
@@ -2002,7 +1995,6 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
             if (lane == 0 && x) atomicAdd(reinterpret_cast<unsigned long long*>(P.counters) + k, x);
         }
     }
-    signal_done(P);
 }
 
 #if !RT_STRICT

@@ -198,9 +198,9 @@ class PeerFrame:
     (rt_kernel.cuh, glsl:404 imageStore) land directly in that buffer over NVLink.
 
     No collective on the frame's path at all.  Behind the frame sit world + 1 32-bit words in the same
-    allocation: word r is raised to the frame's epoch by the LAST CTA of rank r's kernel once all its stores
-    are visible system-wide (rt_options.done_flag; rt_kernel.cuh signal_done), and `dst` puts one warp on its
-    stream that waits for all of them (rt_wait_flags).  The last word runs the other way: `dst` raises it to
+    allocation: word r is raised to the frame's epoch by a one-thread kernel queued behind rank r's render kernel
+    (rt_options.done_flag: every store of the render is visible at the kernel boundary, the word follows with
+    system-scope release), and `dst` puts one warp on its stream that waits for all of them (rt_wait_flags).  The last word runs the other way: `dst` raises it to
     k - 1 when the caller asks for frame k (the previous frame is then his to overwrite), and every producer's
     stream waits for it before its kernel may store -- so a fast rank never writes into a frame `dst` still
     reads.  Setup (IPC handle exchange) uses torch.distributed once; frames do not."""

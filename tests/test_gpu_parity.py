@@ -564,7 +564,7 @@ def test_shaded_light_counter(tracer):
 
 
 def test_completion_flag_and_wait(tracer):
-    """rt_options.done_flag / rt_wait_flags / rt_write_flag on one GPU: the launch's last CTA raises the word to the
+    """rt_options.done_flag / rt_wait_flags / rt_write_flag on one GPU: a one-thread kernel behind the render raises the word to the
     epoch after all framebuffer stores; a wait queued behind it passes; a wait for an epoch nobody raises gives up
     after its timeout instead of hanging the device (multi-GPU frame mode, multigpu.PeerFrame)."""
     import torch
