@@ -147,7 +147,8 @@ typedef struct rt_options {
                                * tests (each warp scans the scene for its own packets); bit 4 = CTA-level packet tests
                                * also below RT_BLOCK_MIN_OBJECTS objects (test switch); bit 5 = shadow packets without
                                * their fan planes (cone and reach only); bit 6 = bounce rays are not grouped into
-                               * packets (per-ray loops) */
+                               * packets (per-ray loops); bit 7 = small scenes: shadow rays that start inside a first box
+                               * that holds every lit light (the room) are tested against it all the same */
     void* done_flag;          /* optional device pointer to a 32-bit completion word -- typically in ANOTHER GPU's memory,
                                * mapped with rt_ipc_import: done_value is stored there (system-scope release, a one-thread
                                * kernel in stream order behind the render) once every framebuffer store of the call is

@@ -16,6 +16,7 @@
 #define RT_DEVICE_H
 
 #include <stdint.h>
+#include <vector_types.h>
 
 /* same value as RT_MAX_DEPTH in include/rt_b200.h (checked in rt_host.cpp) */
 #define RT_MAX_DEPTH_DEV 15
@@ -38,8 +39,13 @@
 #define RT_BLOCK_MAX_OBJECTS_BOUNCE 4096
 #define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
 
-/* Cold record: 64 words. */
+/* Cold record: 64 words; the four material colours first so that each is one aligned 16-byte load. */
 struct RtCold {
+    /* material (glsl:56-69) */
+    float ambient[4];
+    float diffuse[4];
+    float specular[4];
+    float emissive[4];
     float w2l[12];      /* world->local rows: row i = (m[0][i], m[1][i], m[2][i], m[3][i]) of inverse(T*R), glsl:652 */
     float l2w[12];      /* local->world rows, glsl:650 */
     float nmat[9];      /* transpose(inverse(mat3(l2w))), column-major c[col][row], glsl:718 */
@@ -48,11 +54,6 @@ struct RtCold {
     float unused_[4];
     int32_t kind;
     int32_t hot_index;  /* index in the box / sphere hot list */
-    /* material (glsl:56-69) */
-    float ambient[4];
-    float diffuse[4];
-    float specular[4];
-    float emissive[4];
     float shininess;
     float reflectivity;
     float transparency;
@@ -121,6 +122,8 @@ struct RtParams {
     float group_cos;            /* bounce rays join a group when their direction is within this cosine of the leader's */
     float group_k;              /* > 0: secondary rays are traced as grouped packets; group radius^2 = E^2 * group_k */
     uint32_t* blk_log;          /* block kernel, instrumented twin only (RT_BLOCK_LOG=path): 16 words per block, see tools/block_log.py */
+    int32_t room_skip;          /* 1: hot box 0 holds every lit light (with margin): shadow rays that start inside it too skip it */
+    float4 lit_pos[3], lit_dif[3], lit_spc[3];   /* the lit lights (n_lit_batch of them): position, diffuse, specular (glsl:190-196) */
 };
 
 #endif

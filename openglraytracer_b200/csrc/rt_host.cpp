@@ -154,11 +154,13 @@ struct rt_context {
     const RtCold* p_cold = nullptr;
     const RtLightDev* p_lights = nullptr;
     const unsigned int* p_extent = nullptr;
+    int room_skip = 0;                        // hot box 0 holds every lit light (host prologue only)
     // uploaded scene
     bool have_scene = false;
     int n_box = 0, n_sph = 0, n_lights = 0, max_depth = 0, n_lit = 0;
     int n_lit_total = 0, lit[3] = {0, 0, 0};
     float amb_sum[4] = {0, 0, 0, 0};
+    float4 lit_pos[3], lit_dif[3], lit_spc[3];
 };
 
 namespace {
@@ -392,9 +394,32 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     c->n_lit = hs.n_lit;
     c->n_lit_total = hs.n_lit_total;
     memcpy(c->lit, hs.lit, sizeof(c->lit)); memcpy(c->amb_sum, hs.amb_sum, sizeof(c->amb_sum));
+    for (int k = 0; k < 3; k++) {
+        const bool on = k < hs.n_lit_total && hs.n_lit_total <= 3;
+        const RtLightDev z = {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}};
+        const RtLightDev& L = on ? hs.lights[hs.lit[k]] : z;
+        c->lit_pos[k] = make_float4(L.position[0], L.position[1], L.position[2], 0.0f);
+        c->lit_dif[k] = make_float4(L.diffuse[0], L.diffuse[1], L.diffuse[2], L.diffuse[3]);
+        c->lit_spc[k] = make_float4(L.specular[0], L.specular[1], L.specular[2], L.specular[3]);
+    }
     c->max_depth = hs.max_depth;
     c->have_scene = true;
     c->strict_ready = true;
+    // does the first box hold every lit light, 1e-3 (of the half extent) away from its faces?  (all_objects: room_skip)
+    c->room_skip = 0;
+    if (!hs.box_obj.empty() && hs.n_lit_total > 0) {
+        bool all_in = true;
+        const float* r = &hs.box_fast[0];
+        for (const RtLightDev& L : hs.lights) {
+            if (L.position[3] == 0.0f) continue;          // unlit: casts no traversed shadow ray
+            for (int a = 0; a < 3; a++) {
+                const double v = (double)r[4 * a] * L.position[0] + (double)r[4 * a + 1] * L.position[1] +
+                                 (double)r[4 * a + 2] * L.position[2] + (double)r[4 * a + 3];
+                all_in = all_in && std::fabs(v) < 0.999;
+            }
+        }
+        c->room_skip = all_in ? 1 : 0;
+    }
     return RT_OK;
 }
 
@@ -445,9 +470,18 @@ static int upload_device(rt_context* c, const rt_scene* scene) {
     c->n_lit = hs.n_lit;
     c->n_lit_total = hs.n_lit_total;
     memcpy(c->lit, hs.lit, sizeof(c->lit)); memcpy(c->amb_sum, hs.amb_sum, sizeof(c->amb_sum));
+    for (int k = 0; k < 3; k++) {
+        const bool on = k < hs.n_lit_total && hs.n_lit_total <= 3;
+        const RtLightDev z = {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}};
+        const RtLightDev& L = on ? hs.lights[hs.lit[k]] : z;
+        c->lit_pos[k] = make_float4(L.position[0], L.position[1], L.position[2], 0.0f);
+        c->lit_dif[k] = make_float4(L.diffuse[0], L.diffuse[1], L.diffuse[2], L.diffuse[3]);
+        c->lit_spc[k] = make_float4(L.specular[0], L.specular[1], L.specular[2], L.specular[3]);
+    }
     c->max_depth = hs.max_depth;
     c->have_scene = true;
     c->strict_ready = false;
+    c->room_skip = 0;
     return RT_OK;
 }
 
@@ -557,6 +591,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         P.group_cos = group_cos;
     }
     P.extent = reinterpret_cast<const float*>(c->p_extent);
+    P.room_skip = (c->room_skip && !o.strict && !(o.no_cull & 128)) ? 1 : 0;     // bit 7 (test switch): no inside-box shadow skip
     if (P.block) {
         // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
         P.blist_stride = c->n_box + c->n_sph;
@@ -566,6 +601,8 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.n_lit = (P.cull && !P.packet && !(o.no_cull & 2)) ? c->n_lit : 0;
     P.n_lit_batch = c->n_lit_total <= 3 ? c->n_lit_total : -1;
     memcpy(P.lit, c->lit, sizeof(P.lit)); memcpy(P.amb_sum, c->amb_sum, sizeof(P.amb_sum));
+    memcpy(P.lit_pos, c->lit_pos, sizeof(P.lit_pos)); memcpy(P.lit_dif, c->lit_dif, sizeof(P.lit_dif));
+    memcpy(P.lit_spc, c->lit_spc, sizeof(P.lit_spc));
     size_t hot_bytes = ((size_t)P.n_box * (o.strict ? RT_BOX_F4_STRICT : (P.cull ? 1 : RT_BOX_F4_FAST)) + P.n_sph) * 16;
     if (P.n_lit > 0) hot_bytes += (size_t)((P.n_box + P.n_sph + 63) / 64) * P.n_lit * 64 * 16;
     P.resident = hot_bytes <= (o.strict ? rt_strict::resident_limit_bytes(c->max_smem_optin, false)

@@ -1045,7 +1045,25 @@ template <int R, bool ANYHIT, bool SHARED, bool COUNT>
 __device__ __forceinline__ void all_objects(const RtParams& P, const WarpCtx& w,
                                             const V3 (&o)[kShadowBatch], const V3 (&d)[kShadowBatch],
                                             float (&best)[kShadowBatch], int (&bidx)[kShadowBatch], RtCounters& cnt) {
-    boxes_tile<R, ANYHIT, SHARED, COUNT, false>(smem_f4 + w.box_off4, P.n_box, 0, o, d, best, bidx, cnt.box_tests);
+    int first = 0;
+#if !RT_STRICT
+    if (ANYHIT && SHARED && P.room_skip) {                         // uniform: a property of the scene
+        // The first box holds every lit light (the room around the built-in scene; host prologue, with margin).  A
+        // shadow ray that starts inside it as well runs inside it all the way to its light: the exit lies beyond
+        // t = 1 and the test cannot succeed (glsl:690-696: inside -> t = t_far; glsl:816 wants t < 1).  When that holds
+        // for every live ray of the warp the box is left out -- shadow rays are any-hit, their order is free.
+        // 0.99999: away from the last bits of the slab test's own rounding.
+        const float4* __restrict__ rp = smem_f4 + w.box_off4;
+        const float4 rec[RT_BOX_F4] = {rp[0], rp[1], rp[2]};
+        const V3 so = box_origin(rec, o[0]);
+        bool live = false;
+#pragma unroll
+        for (int r = 0; r < R; ++r) live = live || best[r] >= 1.0f;
+        const bool in = fmaxf(fmaxf(fabsf(so.x), fabsf(so.y)), fabsf(so.z)) < 0.99999f;
+        if (__all_sync(kFull, in || !live)) first = 1;
+    }
+#endif
+    boxes_tile<R, ANYHIT, SHARED, COUNT, false>(smem_f4 + w.box_off4 + first * RT_BOX_F4, P.n_box - first, first, o, d, best, bidx, cnt.box_tests);
     spheres_tile<R, ANYHIT, SHARED, COUNT, false>(P, smem_f4 + w.sph_off4, P.n_sph, 0, o, d, best, bidx, cnt);
 }
 
@@ -1437,6 +1455,49 @@ __device__ __forceinline__ uint32_t unorm8(float f) {
 // One sample: recursive_raytrace (glsl:1071-1105) as a weighted pending-ray stack.
 // All 32 lanes run the loop together; a lane without work rides along inactive.
 // -------------------------------------------------------------------------
+// -------------------------------------------------------------------------
+// ads_phong_lighting's light loop (glsl:797-834) for a small scene whose 1..3 lit lights ride in the kernel
+// parameters: NS shadow rays with the shared origin through all_objects, then the diffuse / specular terms of the
+// lights that are not occluded -- straight-line code, light data as constant-bank operands.  Same arithmetic as the
+// general path in trace_sample.
+// -------------------------------------------------------------------------
+template <int NS, bool COUNT>
+__device__ __forceinline__ void shade_small(const RtParams& P, const WarpCtx& w, const Hit& h, const RtCold* __restrict__ mat,
+                                            V3 view, bool shade, float (&dif)[4], float (&spc)[4], RtCounters& cnt) {
+    V3 o[kShadowBatch], d[kShadowBatch];
+    float best[kShadowBatch]; int bidx[kShadowBatch];
+    const V3 so = shade ? axpy3(h.n, 0.01f, h.p) : mk(0.0f, 0.0f, 0.0f);                    // glsl:808
+#pragma unroll
+    for (int r = 0; r < kShadowBatch; ++r) {
+        o[r] = so; bidx[r] = -1;
+        if (r < NS) {
+            const float4 lp = P.lit_pos[r];
+            d[r] = shade ? mk(lp.x - h.p.x, lp.y - h.p.y, lp.z - h.p.z) : mk(0.0f, 0.0f, 1.0f);   // glsl:809
+            best[r] = shade ? 1.0f : 0.0f;                                                   // glsl:816: shadowed iff closest t < 1
+        } else {
+            d[r] = mk(0.0f, 0.0f, 1.0f); best[r] = 0.0f;
+        }
+    }
+    all_objects<NS, true, true, COUNT>(P, w, o, d, best, bidx, cnt);
+    const float4 md = *reinterpret_cast<const float4*>(mat->diffuse), ms = *reinterpret_cast<const float4*>(mat->specular);
+    const float shin = mat->shininess;
+#pragma unroll
+    for (int r = 0; r < NS; ++r) {
+        if (shade && !(best[r] < 1.0f)) {
+            if (COUNT) cnt.shaded_lights++;
+            const V3 light_dir = normalize3(d[r]);                                           // glsl:804
+            const V3 light_ref = normalize3(reflect3(-light_dir, h.n));                      // glsl:825
+            const float cos_theta = dot3(light_dir, h.n);                                    // glsl:826
+            const float cos_phi = dot3(view, light_ref);                                     // glsl:827
+            const float kd = fmaxf(cos_theta, 0.0f);
+            const float ks = fpow(fmaxf(cos_phi, 0.0f), shin);                               // glsl:832
+            const float4 ld4 = P.lit_dif[r], ls4 = P.lit_spc[r];
+            dif[0] += ld4.x * md.x * kd; dif[1] += ld4.y * md.y * kd; dif[2] += ld4.z * md.z * kd; dif[3] += ld4.w * md.w * kd;   // glsl:830
+            spc[0] += ls4.x * ms.x * ks; spc[1] += ls4.y * ms.y * ks; spc[2] += ls4.z * ms.z * ks; spc[3] += ls4.w * ms.w * ks;   // glsl:832
+        }
+    }
+}
+
 // Pending rays of one lane: origin, direction, weight, remaining depth.  BOUNCE = false (MAX_RAYTRACE_DEPTH = 0,
 // the shader as shipped, glsl:22): the tree is its root, there is nothing to keep -- no local-memory frame at all.
 template <bool BOUNCE> struct RayStack;
@@ -1553,6 +1614,17 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
             // lights' ambient terms (glsl:801) and listed the lit lights, so there is one shadow batch and
             // no per-node loop over the light list.  Otherwise (strict kernel, > 3 lit lights): the loops.
             const bool one_batch = !RT_STRICT && P.n_lit_batch >= 0;
+            if (!RT_STRICT && !REPACK && one_batch) {
+                // small scenes: one straight-line batch, light data from the kernel parameters
+                if (shade) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) amb[k] = P.amb_sum[k] * mat->ambient[k];
+                    if (COUNT) { cnt.rays += P.n_lights; cnt.shadow_rays += P.n_lights; cnt.pad += P.n_lights - P.n_lit_batch; }
+                }
+                if (P.n_lit_batch == 2) shade_small<2, COUNT>(P, w, h, mat, view, shade, dif, spc, cnt);
+                else if (P.n_lit_batch == 3) shade_small<3, COUNT>(P, w, h, mat, view, shade, dif, spc, cnt);
+                else if (P.n_lit_batch == 1) shade_small<1, COUNT>(P, w, h, mat, view, shade, dif, spc, cnt);
+            } else {
             if (one_batch) {
                 if (shade) {
 #pragma unroll
@@ -1679,6 +1751,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                     }
                 }
             }
+        }   // general path
         }
         if (hit) {
             float pc[4];

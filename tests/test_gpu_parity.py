@@ -596,3 +596,37 @@ def test_completion_flag_and_wait(tracer):
     api.wait_flags(flags.data_ptr() + 12, 1, 5, stream=stream.cuda_stream, timeout_ms=50)     # nobody raises word 3
     stream.synchronize()
     assert api.wait_flags_timed_out()
+
+
+def test_inside_box_shadow_skip_changes_nothing(tracer):
+    """Small scenes: when the first box holds every lit light (the built-in room), shadow rays of a warp whose origins
+    all lie inside it too leave it out (all_objects: room_skip) -- the test could not succeed (t_far > 1).  The frame
+    is byte-identical with the skip on or off (no_cull bit 7), fewer slab tests run; with the camera OUTSIDE the room
+    (shadow origins on its outer faces, mixed warps) and with a first box that holds no light nothing is skipped."""
+    for t, depth in [(0.0, 0), (0.0, 4), (2.5, 3), (3.7, 5), (7.25, 2)]:
+        sc, cam = rt.builtin_scene(t, depth), rt.builtin_camera(t)
+        on, st_on = tracer.render(sc, cam, 480, 270, want_stats=True)
+        off, st_off = tracer.render(sc, cam, 480, 270, want_stats=True, no_cull=128)
+        assert np.array_equal(on, off), (t, depth)
+        assert np.array_equal(on, tracer.render(sc, cam, 480, 270)) and np.array_equal(on, tracer.render(sc, cam, 480, 270, no_cull=128))
+        assert st_on["box_tests"] < st_off["box_tests"] and st_on["rays"] == st_off["rays"]
+        assert st_on["shaded_lights"] == st_off["shaded_lights"]
+    base = rt.builtin_scene(0.0, 3)
+    for half, expect_skip in [(8.0, True), (5.0, False)]:
+        objs = (rt.Object * 5)(*list(base.objects))
+        objs[0].box_mins[:] = [-half] * 3
+        objs[0].box_maxs[:] = [half] * 3                 # camera (radius 10) outside; lights inside only for half = 8
+        sc = rt.SceneData(objs, base.lights, 3)
+        cam = rt.builtin_camera(0.0)
+        on, st_on = tracer.render(sc, cam, 480, 270, want_stats=True)
+        off, st_off = tracer.render(sc, cam, 480, 270, want_stats=True, no_cull=128)
+        assert np.array_equal(on, off), half
+        assert (st_on["box_tests"] < st_off["box_tests"]) == expect_skip
+        _check(on, ob.render(sc, cam, 480, 270), "room half %g" % half, need_edges=False)
+    # a first box that is not a room at all: the tumbling box first, the room last
+    objs = (rt.Object * 5)(base.objects[3], base.objects[1], base.objects[2], base.objects[4], base.objects[0])
+    sc = rt.SceneData(objs, base.lights, 2)
+    on, st_on = tracer.render(sc, rt.builtin_camera(0.0), 320, 180, want_stats=True)
+    off, st_off = tracer.render(sc, rt.builtin_camera(0.0), 320, 180, want_stats=True, no_cull=128)
+    assert np.array_equal(on, off) and st_on["box_tests"] == st_off["box_tests"]
+    _check(on, ob.render(sc, rt.builtin_camera(0.0), 320, 180), "room last")

@@ -10,5 +10,7 @@ ncu --set full --clock-control none --import-source on -k regex:render_ -s 2 -c 
     python tools/prof_scaled.py $N $W $H $D 2 $M > $O/${TAG}_ncu.log 2>&1
 { python tools/ncu_summary.py /tmp/$TAG.ncu-rep; echo; echo "== executed code footprint (tools/ncu_footprint.py) =="; python tools/ncu_footprint.py /tmp/$TAG.ncu-rep;
   echo; echo "== hottest source lines (ncu --page source; share of samples / of executed instructions) =="; python tools/ncu_lines.py /tmp/$TAG.ncu-rep 45; } > $O/$TAG.txt 2>&1
+python tools/ncu_lines.py /tmp/$TAG.ncu-rep 2000 > $O/${TAG}_all_lines.txt 2>&1
+ncu -i /tmp/$TAG.ncu-rep --page source --csv --print-source sass > $O/${TAG}_sass.csv 2>/dev/null
 [ -n "$WL" ] && python tools/ncu_capture_json.py /tmp/$TAG.ncu-rep $WL $TAG > /dev/null
 head -8 $O/$TAG.txt
