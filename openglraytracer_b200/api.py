@@ -46,6 +46,27 @@ class SceneData:
     def objects_count(self):
         return self.scene.objects_count
 
+    def pinned(self):
+        """The same scene with its objects[] in page-locked host memory (rt_host_alloc): large scenes then go up
+        over PCIe straight from the array at full rate (the device prologue copies them in one DMA, no staging)."""
+        n = max(1, len(self.objects))
+        ptr = C.c_void_p()
+        check(_abi.lib().rt_host_alloc(C.byref(ptr), n * C.sizeof(Object)), "rt_host_alloc")
+        objs = (Object * n).from_address(ptr.value)
+        C.memmove(objs, self.objects, len(self.objects) * C.sizeof(Object))
+        out = SceneData(objs, self.lights, self.max_depth)
+        out.scene.objects_count = self.scene.objects_count
+        out.scene.lights_count = self.scene.lights_count
+        out._pinned_ptr = ptr
+        return out
+
+    def free_pinned(self):
+        ptr = getattr(self, "_pinned_ptr", None)
+        if ptr:
+            self.objects = None
+            _abi.lib().rt_host_free(ptr)
+            self._pinned_ptr = None
+
 
 def builtin_scene(time=0.0, max_depth=0):
     """objects[5], lights[3] of the shader at uniform `time` (glsl:199-224, 261-321).

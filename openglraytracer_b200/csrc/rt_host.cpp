@@ -41,10 +41,11 @@ cudaError_t configure(int device, int* max_smem_optin);
 size_t resident_limit_bytes(int max_smem_optin, bool cull);
 }
 namespace rt_prologue {
-cudaError_t run(const rt_object* d_objs, const int32_t* d_kind, const int32_t* d_hot_index, int n_obj,
-                int n_box, int n_sph, RtCold* d_cold, float* d_box_fast, float* d_box_cull, float* d_sph,
-                const RtLightDev* d_lights, int n_lit, const int* lit, float light_reach,
-                unsigned int* d_extent_bits, float* d_obj_lrec, cudaStream_t st);
+int max_grid(int sm_count);
+size_t scratch_bytes(int max_ctas);
+cudaError_t run(const rt_object* d_objs, int n_obj, int32_t* d_box_obj, int32_t* d_sph_obj, RtCold* d_cold,
+                float* d_box_fast, float* d_box_cull, float* d_sph, const RtLightDev* d_lights, int n_lit, const int* lit,
+                float light_reach, float* d_obj_lrec, void* d_scratch, int sm_count, cudaStream_t st);
 }
 namespace rt_strict {
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
@@ -131,14 +132,14 @@ struct rt_context {
     DevBuf<uint8_t> d_out;
     DevBuf<RtCounters> d_cnt;
     DevBuf<unsigned long long> d_tile;
-    DevBuf<rt_object> d_objs;                 // device prologue inputs
-    DevBuf<int32_t> d_kind, d_hot;
-    DevBuf<unsigned int> d_extent;
+    DevBuf<rt_object> d_objs;                 // device prologue: the raw objects
+    DevBuf<uint8_t> d_scratch;                // device prologue: counts, extent, barrier words
+    size_t n_objects_dev = 0;
     DevBuf<uint32_t> d_blist;                 // block kernel: shadow-candidate lists, one slice per resident CTA
     DevBuf<uint32_t> d_blklog;                // block kernel, RT_BLOCK_LOG=path: per-block timing records of the instrumented twin
     int prologue_mode = RT_PROLOGUE_AUTO;
     bool strict_ready = false;                // d_box_strict holds the current scene
-    std::vector<rt_object> objs_copy;
+    std::vector<rt_object> objs_copy;         // strict render after a device prologue: fetched back from d_objs
     std::vector<rt_light> lights_copy;
     int depth_copy = 0;
     uint8_t* h_pinned = nullptr;
@@ -165,18 +166,9 @@ struct rt_context {
 
 namespace {
 
-// Classification (glsl:749, 759) and the hot lists in original order; cheap, always on the host.
-void classify_scene(const rt_scene* scene, HostScene* hs) {
-    const int n = scene->objects_count;
-    hs->kind.assign(n > 0 ? n : 0, RT_KIND_SKIP);
-    hs->hot_index.assign(n > 0 ? n : 0, -1);
-    hs->box_obj.clear(); hs->sph_obj.clear();
-    for (int i = 0; i < n; i++) {
-        const int k = rtpm::object_kind(scene->objects[i]);
-        hs->kind[i] = k;
-        if (k == RT_KIND_BOX) { hs->hot_index[i] = (int32_t)hs->box_obj.size(); hs->box_obj.push_back(i); }
-        else if (k == RT_KIND_SPHERE) { hs->hot_index[i] = (int32_t)hs->sph_obj.size(); hs->sph_obj.push_back(i); }
-    }
+// The lights: device records, the lit ones (a light with zero diffuse and specular adds 0 shadowed or not, glsl:830-832),
+// the ambient sum (glsl:801), max |light position| (part of the scene extent).
+void classify_lights(const rt_scene* scene, HostScene* hs) {
     hs->max_depth = scene->max_depth;
     hs->lights.resize(scene->lights_count > 0 ? scene->lights_count : 0);
     std::vector<int> lit;
@@ -188,7 +180,7 @@ void classify_scene(const rt_scene* scene, HostScene* hs) {
         memcpy(d.ambient, L.ambient, 16);
         memcpy(d.diffuse, L.diffuse, 16);
         memcpy(d.specular, L.specular, 16);
-        bool is_lit = false;   // a light with zero diffuse and specular adds 0 shadowed or not (glsl:830-832)
+        bool is_lit = false;
         for (int k = 0; k < 4; k++) is_lit = is_lit || L.diffuse[k] != 0.0f || L.specular[k] != 0.0f;
         d.position[3] = is_lit ? 1.0f : 0.0f;
         if (is_lit) lit.push_back(j);
@@ -207,6 +199,21 @@ void classify_scene(const rt_scene* scene, HostScene* hs) {
         const float zero[3] = {L.position[0], L.position[1], L.position[2]};
         hs->light_reach = std::max(hs->light_reach, rtpm::reach(zero, 0.0));
     }
+}
+
+// Classification (glsl:749, 759) and the hot lists in original order (host prologue).
+void classify_scene(const rt_scene* scene, HostScene* hs) {
+    const int n = scene->objects_count;
+    hs->kind.assign(n > 0 ? n : 0, RT_KIND_SKIP);
+    hs->hot_index.assign(n > 0 ? n : 0, -1);
+    hs->box_obj.clear(); hs->sph_obj.clear();
+    for (int i = 0; i < n; i++) {
+        const int k = rtpm::object_kind(scene->objects[i]);
+        hs->kind[i] = k;
+        if (k == RT_KIND_BOX) { hs->hot_index[i] = (int32_t)hs->box_obj.size(); hs->box_obj.push_back(i); }
+        else if (k == RT_KIND_SPHERE) { hs->hot_index[i] = (int32_t)hs->sph_obj.size(); hs->sph_obj.push_back(i); }
+    }
+    classify_lights(scene, hs);
 }
 
 // Host prologue: per-object matrices and records (rt_prologue_math.h), then the padded bounding records.
@@ -315,7 +322,7 @@ int rt_destroy(rt_context* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_obj_lrec.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
-    c->d_objs.release(); c->d_kind.release(); c->d_hot.release(); c->d_extent.release(); c->d_blist.release(); c->d_blklog.release();
+    c->d_objs.release(); c->d_scratch.release(); c->d_blist.release(); c->d_blklog.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -423,49 +430,46 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     return RT_OK;
 }
 
-// Device prologue (rt_prologue.cu): classification on the host, raw objects over PCIe, records built
-// in HBM.  Fast kernel only; a later strict render re-runs the host prologue from the kept copy.
+// Device prologue (rt_prologue.cu): the raw objects go up in one copy straight from the caller's array, one kernel
+// classifies them, assigns the hot-list positions and builds every record in HBM.  Fast kernel only; a later strict
+// render fetches the objects back and re-runs the host prologue.
 static int upload_device(rt_context* c, const rt_scene* scene) {
     HostScene hs;
-    classify_scene(scene, &hs);
+    classify_lights(scene, &hs);
     const size_t n = (size_t)(scene->objects_count > 0 ? scene->objects_count : 0);
-    const size_t nb = hs.box_obj.size(), ns = hs.sph_obj.size();
     CU(cudaSetDevice(c->device));
+    // The previous frame may still be reading these buffers -- on the context's stream or on a caller's.
     CU(cudaStreamSynchronize(c->stream));
     if (c->render_recorded) CU(cudaEventSynchronize(c->ev_render));
+    const int grid_cap = rt_prologue::max_grid(c->sm_count);
     CU(c->d_objs.reserve(n + 1));
-    CU(c->d_kind.reserve(n + 1));
-    CU(c->d_hot.reserve(n + 1));
-    CU(c->d_extent.reserve(1));
-    CU(c->d_box_fast.reserve(nb * 12 + 4));
-    CU(c->d_box_cull.reserve(nb * 4 + 4));
-    CU(c->d_obj_lrec.reserve(((nb + ns + 63) / 64) * (size_t)(hs.n_lit > 0 ? hs.n_lit : 1) * 64 * 4 + 4));
-    CU(c->d_sph.reserve(ns * 4 + 4));
-    CU(c->d_box_obj.reserve(nb + 1));
-    CU(c->d_sph_obj.reserve(ns + 1));
+    CU(c->d_scratch.reserve(rt_prologue::scratch_bytes(grid_cap)));
+    CU(c->d_box_fast.reserve(n * 12 + 4));
+    CU(c->d_box_cull.reserve(n * 4 + 4));
+    CU(c->d_obj_lrec.reserve(((n + 63) / 64) * (size_t)(hs.n_lit > 0 ? hs.n_lit : 1) * 64 * 4 + 4));
+    CU(c->d_sph.reserve(n * 4 + 4));
+    CU(c->d_box_obj.reserve(n + 1));
+    CU(c->d_sph_obj.reserve(n + 1));
     CU(c->d_cold.reserve(n + 1));
     CU(c->d_lights.reserve(hs.lights.size() + 1));
-    auto up = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
-        if (bytes == 0) return cudaSuccess;
-        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
-    };
-    CU(up(c->d_objs.p, scene->objects, n * sizeof(rt_object)));
-    CU(up(c->d_kind.p, hs.kind.data(), n * 4));
-    CU(up(c->d_hot.p, hs.hot_index.data(), n * 4));
-    CU(up(c->d_box_obj.p, hs.box_obj.data(), nb * 4));
-    CU(up(c->d_sph_obj.p, hs.sph_obj.data(), ns * 4));
-    CU(up(c->d_lights.p, hs.lights.data(), hs.lights.size() * sizeof(RtLightDev)));
-    CU(rt_prologue::run(c->d_objs.p, c->d_kind.p, c->d_hot.p, (int)n, (int)nb, (int)ns, c->d_cold.p, c->d_box_fast.p,
-                        c->d_box_cull.p, c->d_sph.p, c->d_lights.p, hs.n_lit, hs.lit, (float)hs.light_reach,
-                        c->d_extent.p, c->d_obj_lrec.p, c->stream));
-    g_launches += 2 + (hs.n_lit > 0 ? 1 : 0);
-    CU(cudaStreamSynchronize(c->stream));   // the host vectors above go out of scope
+    if (n) CU(cudaMemcpyAsync(c->d_objs.p, scene->objects, n * sizeof(rt_object), cudaMemcpyHostToDevice, c->stream));
+    if (!hs.lights.empty())
+        CU(cudaMemcpyAsync(c->d_lights.p, hs.lights.data(), hs.lights.size() * sizeof(RtLightDev), cudaMemcpyHostToDevice, c->stream));
+    CU(rt_prologue::run(c->d_objs.p, (int)n, c->d_box_obj.p, c->d_sph_obj.p, c->d_cold.p, c->d_box_fast.p, c->d_box_cull.p,
+                        c->d_sph.p, c->d_lights.p, hs.n_lit, hs.lit, (float)hs.light_reach, c->d_obj_lrec.p, c->d_scratch.p,
+                        c->sm_count, c->stream));
+    g_launches += 1;
+    unsigned int back[3] = {0, 0, 0};      // n_box, n_sph, extent bits
+    CU(cudaMemcpyAsync(back, c->d_scratch.p, sizeof(back), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));   // the counts size the render launch; the caller's array is free again
     c->upload_recorded = false;             // complete: nothing for a caller's stream to wait for
-    c->p_extent = c->d_extent.p; c->p_box_fast = c->d_box_fast.p; c->p_box_strict = nullptr; c->p_box_cull = c->d_box_cull.p;
+    c->p_extent = reinterpret_cast<const unsigned int*>(c->d_scratch.p) + 2;
+    c->p_box_fast = c->d_box_fast.p; c->p_box_strict = nullptr; c->p_box_cull = c->d_box_cull.p;
     c->p_obj_lrec = c->d_obj_lrec.p; c->p_sph = c->d_sph.p; c->p_box_obj = c->d_box_obj.p; c->p_sph_obj = c->d_sph_obj.p;
     c->p_cold = c->d_cold.p; c->p_lights = c->d_lights.p;
-    c->n_box = (int)nb;
-    c->n_sph = (int)ns;
+    c->n_box = (int)back[0];
+    c->n_sph = (int)back[1];
+    c->n_objects_dev = n;
     c->n_lights = (int)hs.lights.size();
     c->n_lit = hs.n_lit;
     c->n_lit_total = hs.n_lit_total;
@@ -496,12 +500,14 @@ int rt_upload_scene(rt_context* c, const rt_scene* scene) {
     if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
     int rc = validate_scene(scene);
     if (rc != RT_OK) return rc;
-    // keep the scene: a strict render after a device prologue needs the host records
-    c->objs_copy.assign(scene->objects, scene->objects + (scene->objects_count > 0 ? scene->objects_count : 0));
-    c->lights_copy.assign(scene->lights, scene->lights + (scene->lights_count > 0 ? scene->lights_count : 0));
-    c->depth_copy = scene->max_depth;
     const bool dev = c->prologue_mode == RT_PROLOGUE_DEVICE ||
                      (c->prologue_mode == RT_PROLOGUE_AUTO && scene->objects_count >= RT_PROLOGUE_DEVICE_MIN_OBJECTS);
+    if (dev) {
+        // a strict render after a device prologue needs the host records: the lights are kept, the objects stay
+        // on the device (d_objs) and are fetched back only then
+        c->lights_copy.assign(scene->lights, scene->lights + (scene->lights_count > 0 ? scene->lights_count : 0));
+        c->depth_copy = scene->max_depth;
+    }
     return dev ? upload_device(c, scene) : upload_host(c, scene);
 }
 
@@ -511,6 +517,11 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     if (!c->have_scene) return fail(RT_ERR_BAD_ARG, "no scene uploaded");
     if (opts_in && opts_in->strict && !c->strict_ready) {
         // the scene went through the device prologue: the strict kernel wants the host run's records
+        c->objs_copy.resize(c->n_objects_dev);
+        CU(cudaSetDevice(c->device));
+        CU(cudaStreamSynchronize(c->stream));
+        if (c->n_objects_dev)
+            CU(cudaMemcpy(c->objs_copy.data(), c->d_objs.p, c->n_objects_dev * sizeof(rt_object), cudaMemcpyDeviceToHost));
         rt_scene sc;
         sc.objects = c->objs_copy.data(); sc.objects_count = (int32_t)c->objs_copy.size();
         sc.lights = c->lights_copy.data(); sc.lights_count = (int32_t)c->lights_copy.size();
