@@ -103,11 +103,14 @@ __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, con
     rayset_load(rs, o_in, d_in, best_io, bidx_io);
     const Cone cone = cone_in[0];
     const int lane = w.lane;
+    // GLOB: the list was written to global memory by this CTA during this launch: coherent (L2) loads, the next 32
+    // entries in flight while the current ones are tested
+    uint32_t ent_next = lane < count ? (GLOB ? __ldcg(list + lane) : list[lane]) : 0u;
     for (int e0 = 0; e0 < count; e0 += 32) {
         if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
         const int e = e0 + lane;
-        // GLOB: the list was written to global memory by this CTA during this launch: coherent (L2) loads
-        const uint32_t ent = e < count ? (GLOB ? __ldcg(list + e) : list[e]) : 0u;
+        const uint32_t ent = ent_next;
+        ent_next = e + 32 < count ? (GLOB ? __ldcg(list + e + 32) : list[e + 32]) : 0u;
         const int hot = (int)(ent & 0x0fffffffu);
         const bool sel = e < count && ((ent >> 28) & kbit) != 0u;
         const bool sph = hot >= P.n_box;
@@ -327,30 +330,34 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 // wall) would blow the cone up; they go into a ball around the light instead: a shadow ray that
                 // starts within r of L and runs toward L stays within r of L.  near = closer than a quarter of the
                 // warp's mean distance; each warp may classify as it likes, every point lands in the cone or the ball.
-                V3 u[kShadowBatch][kShadowBatch];        // [light][tile]
-                float l2[kShadowBatch][kShadowBatch];
-                bool nearp[kShadowBatch][kShadowBatch];
+                // (unit directions and distances are recomputed where they are needed instead of living in 45 registers
+                // across the CTA barriers; `thr` is all a later pass needs to classify a point again)
+                float thr[kShadowBatch];
+                auto light_vec = [&](int k, int q, V3& uq, float& l2q) {
+                    const V3 v = hp[q] - lp[k];
+                    l2q = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
+                    uq = v * rsqrtf(l2q);
+                };
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
                     float dsum = 0.0f, dn = 0.0f;
+                    V3 u[kShadowBatch]; float l2[kShadowBatch];
 #pragma unroll
                     for (int q = 0; q < kShadowBatch; ++q) {
-                        const V3 v = hp[q] - lp[k];
-                        l2[k][q] = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
-                        u[k][q] = v * rsqrtf(l2[k][q]);
-                        if (sh[q]) { dsum += sqrt_approx(l2[k][q]); dn += 1.0f; }
+                        light_vec(k, q, u[q], l2[q]);
+                        if (sh[q]) { dsum += sqrt_approx(l2[q]); dn += 1.0f; }
                     }
 #pragma unroll
                     for (int off = 16; off > 0; off >>= 1) {
                         dsum += __shfl_xor_sync(kFull, dsum, off);
                         dn += __shfl_xor_sync(kFull, dn, off);
                     }
-                    const float thr = dn > 0.0f ? 0.25f * dsum / dn : 0.0f;
+                    thr[k] = dn > 0.0f ? 0.25f * dsum / dn : 0.0f;
                     float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
                     for (int q = 0; q < kShadowBatch; ++q) {
-                        nearp[k][q] = sh[q] && l2[k][q] < thr * thr;
-                        if (sh[q] && !nearp[k][q] && k < n_lights_b) { acc[0] += u[k][q].x; acc[1] += u[k][q].y; acc[2] += u[k][q].z; acc[3] += 1.0f; }
+                        const bool nearq = sh[q] && l2[q] < thr[k] * thr[k];
+                        if (sh[q] && !nearq && k < n_lights_b) { acc[0] += u[q].x; acc[1] += u[q].y; acc[2] += u[q].z; acc[3] += 1.0f; }
                     }
 #pragma unroll
                     for (int off = 16; off > 0; off >>= 1) {
@@ -382,15 +389,18 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     const V3 bn = fan_normal(bc[0].axis, org - lp[k]);      // the block's fan plane: through the light and the block's view axis
 #pragma unroll
                     for (int q = 0; q < kShadowBatch; ++q) {
-                        const V3 x = cross3(lc[k].axis, u[k][q]);
+                        V3 uq; float l2q;
+                        light_vec(k, q, uq, l2q);
+                        const bool nearq = sh[q] && l2q < thr[k] * thr[k];
+                        const V3 x = cross3(lc[k].axis, uq);
                         const float s2q = __fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z)));
-                        if (sh[q] && !nearp[k][q]) {
+                        if (sh[q] && !nearq) {
                             s2 = fmaxf(s2, fminf(s2q, 1.0f));
-                            lmax = fmaxf(lmax, l2[k][q]);
-                            in_cone = in_cone && dot3(lc[k].axis, u[k][q]) >= kBlockMinCos;    // NaN -> false
+                            lmax = fmaxf(lmax, l2q);
+                            in_cone = in_cone && dot3(lc[k].axis, uq) >= kBlockMinCos;    // NaN -> false
                             hmax = fmaxf(hmax, fabsf(dot3(bn, hp[q] - lp[k])));
                         }
-                        if (nearp[k][q] && k < n_lights_b) nmax = fmaxf(nmax, l2[k][q]);
+                        if (nearq && k < n_lights_b) nmax = fmaxf(nmax, l2q);
                     }
                     const float s2w = warp_max_nonneg(s2), lw = warp_max_nonneg(lmax), nw = warp_max_nonneg(nmax);
                     const float hwp = warp_max_nonneg(hmax < 1e30f ? hmax : 1e30f);                // NaN -> no plane
@@ -444,7 +454,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                                 sbk[q] = sh[q] ? 1.0f : 0.0f;
                                 ll[q] = __fmaf_rn(sd3[q].x, sd3[q].x, __fmaf_rn(sd3[q].y, sd3[q].y, __fmul_rn(sd3[q].z, sd3[q].z)));
                                 uu[q] = sd3[q] * -rsqrtf(ll[q]);
-                                nq[q] = k == 0 ? nearp[0][q] : (k == 1 ? nearp[1][q] : nearp[2][q]);
+                                const float thk = k == 0 ? thr[0] : (k == 1 ? thr[1] : thr[2]);
+                                nq[q] = sh[q] && ll[q] < thk * thk;
                                 if (sh[q] && !nq[q]) sm = sm + uu[q];
                             }
 #pragma unroll
