@@ -613,10 +613,12 @@ def test_inside_box_shadow_skip_changes_nothing(tracer):
         assert st_on["box_tests"] < st_off["box_tests"] and st_on["rays"] == st_off["rays"]
         assert st_on["shaded_lights"] == st_off["shaded_lights"]
     base = rt.builtin_scene(0.0, 3)
-    for half, expect_skip in [(8.0, True), (5.0, False)]:
+    # half 10.5: camera (radius 10 orbit, at (8.8, 4.8, 0)) and lights inside -> skipped; half 8: lights inside but the
+    # camera, hence every shadow origin (outer faces of the room), outside -> nothing to skip; half 5: lights outside
+    for half, expect_skip in [(10.5, True), (8.0, False), (5.0, False)]:
         objs = (rt.Object * 5)(*list(base.objects))
         objs[0].box_mins[:] = [-half] * 3
-        objs[0].box_maxs[:] = [half] * 3                 # camera (radius 10) outside; lights inside only for half = 8
+        objs[0].box_maxs[:] = [half] * 3
         sc = rt.SceneData(objs, base.lights, 3)
         cam = rt.builtin_camera(0.0)
         on, st_on = tracer.render(sc, cam, 480, 270, want_stats=True)
