@@ -210,6 +210,30 @@ int rt_upload_scene(rt_context* ctx, const rt_scene* scene);
 int rt_render_uploaded(rt_context* ctx, const rt_camera* cameras, int n_frames,
                        void* out_rgba, int width, int height, const rt_options* opts);
 
+/* rt_render_block_noalloc -- NO COUNTERPART IN THE REFERENCE.
+ * For callers that must not allocate while rendering (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc): renders n_frames cameras over the scene already uploaded with
+ * rt_upload_scene() into the caller's DEVICE buffer out_rgba_device (layout as rt_render_uploaded with
+ * out_is_device = 1) through the CTA-level packet kernel (render_block_kernel), with all of that kernel's
+ * scratch -- tile counter, camera records, per-CTA shadow-candidate lists -- in ONE file-scope device array of
+ * RT_NOALLOC_SCRATCH_BYTES (8 MiB + 4 KiB; every GPU that loads the library holds it until process exit).
+ * The call makes no cudaMalloc / cudaFree / cudaHostAlloc and calls no allocating library routine; the set-up
+ * (rt_create, rt_upload_scene, the caller's output buffer) is done beforehand and may allocate.
+ * Limits, rejected with RT_ERR_UNSUPPORTED and a message: RT_PACKET objects minimum (96 boxes + spheres: below
+ * that the block kernel is not used at all), at most RT_NOALLOC_MAX_OBJECTS boxes + spheres, at most
+ * RT_NOALLOC_MAX_FRAMES cameras; device output only; fast kernel only (opts->strict, opts->stats and the
+ * no_cull switches 1 / 4 / 8 are refused).  Honoured options: spp, seed, y0 / y1, out_band_only, stream, async,
+ * done_flag / done_value, no_cull bits 5-6.
+ * The array is shared by every call on that GPU and keeps the last call's contents; what must start at zero
+ * (the tile counter) is cleared by each call.  Calls that OVERLAP on the GPU -- two streams, two contexts on one
+ * device, a second call before the first has finished under async -- race on it: serialise them.
+ * Output: byte-identical to rt_render_uploaded on the same scene, cameras and options. */
+#define RT_NOALLOC_MAX_OBJECTS 2048
+#define RT_NOALLOC_MAX_FRAMES 16
+#define RT_NOALLOC_SCRATCH_BYTES (4096 + 4 * 256 * 2048 * 4)
+int rt_render_block_noalloc(rt_context* ctx, const rt_camera* cameras, int n_frames, void* out_rgba_device,
+                            int width, int height, const rt_options* opts);
+
 /* Where the per-object prologue of rt_upload_scene runs (the matrices the shader rebuilds per test,
  * glsl:650-652, 718): on the host, or as device kernels from the raw objects (large animated scenes:
  * 8.6 MB of objects over PCIe instead of 27 MB of records at 64k objects, no host trigonometry).

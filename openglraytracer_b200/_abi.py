@@ -14,6 +14,9 @@ RT_OK = 0
 RT_ERR_BAD_ARG = -1
 RT_ERR_CUDA = -2
 RT_ERR_NO_DEVICE = -3
+RT_ERR_UNSUPPORTED = -5
+RT_NOALLOC_MAX_OBJECTS = 2048
+RT_NOALLOC_MAX_FRAMES = 16
 RT_MAX_DEPTH = 15
 RT_MAX_LIGHTS = 64
 
@@ -72,7 +75,7 @@ class Options(C.Structure):
 EXPORTS = [
     "rt_abi_version", "rt_last_error_string", "rt_kernel_launch_count", "rt_create", "rt_destroy",
     "rt_synchronize", "rt_options_default", "rt_host_alloc", "rt_host_free", "rt_render", "rt_render_ex",
-    "rt_render_batch", "rt_upload_scene", "rt_render_uploaded", "rt_builtin_scene", "rt_builtin_camera",
+    "rt_render_batch", "rt_upload_scene", "rt_render_uploaded", "rt_render_block_noalloc", "rt_builtin_scene", "rt_builtin_camera",
     "rt_orbit_camera", "rt_scaled_scene", "rt_write_ppm", "rt_write_raw", "rt_fp32_peak_tflops",
     "rt_ipc_export", "rt_ipc_import", "rt_ipc_close", "rt_device_alloc", "rt_device_free",
     "rt_wait_flags", "rt_wait_flags_status", "rt_write_flag", "rt_set_prologue", "rt_scene_save", "rt_scene_load", "rt_scene_file_scene", "rt_scene_file_camera", "rt_scene_file_free",
@@ -108,6 +111,7 @@ def lib():
                                   C.POINTER(Options)]
     L.rt_upload_scene.argtypes = [vp, C.POINTER(Scene)]
     L.rt_render_uploaded.argtypes = [vp, C.POINTER(Camera), C.c_int, vp, C.c_int, C.c_int, C.POINTER(Options)]
+    L.rt_render_block_noalloc.argtypes = [vp, C.POINTER(Camera), C.c_int, vp, C.c_int, C.c_int, C.POINTER(Options)]
     L.rt_builtin_scene.argtypes = [C.c_float, C.POINTER(Object), C.POINTER(Light), C.POINTER(Scene)]
     L.rt_builtin_camera.argtypes = [C.c_float, C.POINTER(Camera)]
     L.rt_orbit_camera.argtypes = [C.c_float, C.POINTER(Camera)]

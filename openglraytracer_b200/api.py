@@ -246,6 +246,18 @@ class Raytracer:
         return result
 
 
+def render_block_noalloc(raytracer, camera_uniforms, width, height, out_device_ptr, *, spp=1, seed=0x5EED0001, y0=0, y1=0,
+                         band_only=False, async_=False, stream=None, no_cull=0):
+    """rt_render_block_noalloc: the uploaded scene through the block kernel with all scratch in the library's
+    file-scope device array -- the call allocates nothing (no counterpart in the reference; see include/rt_b200.h)."""
+    batch = isinstance(camera_uniforms, C.Array)
+    n = len(camera_uniforms) if batch else 1
+    cams = C.cast(camera_uniforms if batch else C.byref(camera_uniforms), C.POINTER(Camera))
+    opts = Raytracer._options(spp, seed, y0, y1, False, 1, band_only, async_, stream, None, no_cull)
+    check(_abi.lib().rt_render_block_noalloc(raytracer._ctx, cams, n, C.c_void_p(int(out_device_ptr)), width, height,
+                                             C.byref(opts)), "rt_render_block_noalloc")
+
+
 def fp32_peak_tflops(device=-1, iters=4096):
     """FP32 FMA-chain microbenchmark (2 flop/FMA): roofline denominator check."""
     tf = C.c_double()

@@ -38,6 +38,15 @@
  * 56 ms against 69 ms) */
 #define RT_BLOCK_MAX_OBJECTS_BOUNCE 4096
 #define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
+/* rt_render_block_noalloc: limits of the file-scope scratch array (same values as in include/rt_b200.h, checked in rt_host.cpp) */
+#define RT_NOALLOC_MAX_OBJECTS_DEV 2048
+#define RT_NOALLOC_MAX_FRAMES_DEV 16
+#define RT_NOALLOC_SCRATCH_BYTES_DEV (4096 + 4 * 256 * 2048 * 4)
+#ifndef RT_NOALLOC_MAX_OBJECTS
+#define RT_NOALLOC_MAX_OBJECTS RT_NOALLOC_MAX_OBJECTS_DEV
+#define RT_NOALLOC_MAX_FRAMES RT_NOALLOC_MAX_FRAMES_DEV
+#define RT_NOALLOC_SCRATCH_BYTES RT_NOALLOC_SCRATCH_BYTES_DEV
+#endif
 
 /* Cold record: 64 words; the four material colours first so that each is one aligned 16-byte load. */
 struct RtCold {

@@ -34,8 +34,12 @@ static_assert(sizeof(rt_object) == 33 * 4, "rt_object must be 33 words (glsl:244
 static_assert(sizeof(rt_light) == 15 * 4, "rt_light must be 15 words (glsl:190-196)");
 static_assert(sizeof(rt_camera) == 10 * 4, "rt_camera must be 10 words (glsl:36-50)");
 static_assert(sizeof(RtCold) == 64 * 4, "cold record must be 256 bytes");
+static_assert(RT_NOALLOC_MAX_OBJECTS == RT_NOALLOC_MAX_OBJECTS_DEV && RT_NOALLOC_MAX_FRAMES == RT_NOALLOC_MAX_FRAMES_DEV &&
+              RT_NOALLOC_SCRATCH_BYTES == RT_NOALLOC_SCRATCH_BYTES_DEV, "no-alloc limits out of sync");
 
 namespace rt_fast {
+cudaError_t launch_block_noalloc(const RtParams& P, const RtCameraDev* cams_host, int device, int sm_count,
+                                 cudaStream_t stream, const char** why);
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
 size_t resident_limit_bytes(int max_smem_optin, bool cull);
@@ -719,6 +723,107 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
             if (FILE* f = fopen(blk_log_path, "wb")) { fwrite(hl.data(), 4, blk_log_words, f); fclose(f); }
         }
     }
+    return RT_OK;
+}
+
+// No counterpart in the reference (see include/rt_b200.h).
+// A separate function on purpose: the existing render path is untouched.  Nothing below allocates -- no DevBuf
+// reserve, no std::vector, no host staging: the camera records travel in the set-up kernel's parameters and all
+// device scratch is the file-scope array of rt_kernel_fast.cu.
+int rt_render_block_noalloc(rt_context* c, const rt_camera* cameras, int n_frames, void* out_rgba_device,
+                            int width, int height, const rt_options* opts_in) {
+    if (!c) return fail(RT_ERR_BAD_ARG, "ctx is NULL");
+    if (!c->have_scene) return fail(RT_ERR_BAD_ARG, "no scene uploaded (rt_upload_scene first: the no-alloc call does no set-up)");
+    if (!cameras || n_frames <= 0) return fail(RT_ERR_BAD_ARG, "bad cameras / n_frames");
+    if (!out_rgba_device) return fail(RT_ERR_BAD_ARG, "out_rgba_device is NULL");
+    if (width <= 0 || height <= 0) return fail(RT_ERR_BAD_ARG, "bad image size %dx%d", width, height);
+    rt_options od;
+    rt_options_default(&od);
+    const rt_options& o = opts_in ? *opts_in : od;
+    if (o.strict) return fail(RT_ERR_UNSUPPORTED, "rt_render_block_noalloc: the strict kernel is not available here");
+    if (o.stats) return fail(RT_ERR_UNSUPPORTED, "rt_render_block_noalloc: no counters (rt_options.stats must be NULL)");
+    if (o.no_cull & (1 | 4 | 8)) return fail(RT_ERR_UNSUPPORTED, "rt_render_block_noalloc: no_cull bits 0, 2, 3 switch the block kernel off");
+    const int n_hot = c->n_box + c->n_sph;
+    if (n_frames > RT_NOALLOC_MAX_FRAMES)
+        return fail(RT_ERR_UNSUPPORTED, "rt_render_block_noalloc: %d cameras, the static scratch holds at most RT_NOALLOC_MAX_FRAMES = %d",
+                    n_frames, RT_NOALLOC_MAX_FRAMES);
+    if (n_hot > RT_NOALLOC_MAX_OBJECTS)
+        return fail(RT_ERR_UNSUPPORTED, "rt_render_block_noalloc: %d boxes + spheres, the static scratch holds the candidate lists of at most "
+                    "RT_NOALLOC_MAX_OBJECTS = %d (use rt_render_uploaded)", n_hot, RT_NOALLOC_MAX_OBJECTS);
+    if (n_hot < RT_PACKET_MIN_OBJECTS)
+        return fail(RT_ERR_UNSUPPORTED, "rt_render_block_noalloc: %d boxes + spheres, the block kernel needs at least %d (use rt_render_uploaded)",
+                    n_hot, RT_PACKET_MIN_OBJECTS);
+    const int spp = o.spp > 0 ? o.spp : 1;
+    const int y0 = o.y0 > 0 ? o.y0 : 0;
+    const int y1 = (o.y1 > 0 && o.y1 <= height) ? o.y1 : height;
+    if (y0 >= y1) return fail(RT_ERR_BAD_ARG, "empty row band [%d,%d)", y0, y1);
+    if (o.device >= 0 && o.device != c->device)
+        return fail(RT_ERR_BAD_ARG, "options.device %d != context device %d", o.device, c->device);
+    CU(cudaSetDevice(c->device));
+    cudaStream_t st = o.stream ? (cudaStream_t)o.stream : c->stream;
+    if (st != c->stream && c->upload_recorded) CU(cudaStreamWaitEvent(st, c->ev_upload, 0));
+
+    RtCameraDev cams[RT_NOALLOC_MAX_FRAMES];            // camera prologue (glsl:366-383 hoisted), on the stack
+    for (int k = 0; k < n_frames; k++) {
+        const rt_camera& cam = cameras[k];
+        rthm::inverse_proj_view(cam.position, cam.angles, cam.v_fov, cam.aspect, cam.near_plane, cam.far_plane, cams[k].inv_pv);
+        cams[k].position[0] = cam.position[0]; cams[k].position[1] = cam.position[1];
+        cams[k].position[2] = cam.position[2]; cams[k].position[3] = 1.0f;
+    }
+    const int band_rows = y1 - y0;
+    const bool band_only = o.out_band_only != 0;
+    RtParams P;
+    memset(&P, 0, sizeof(P));
+    P.box_hot = reinterpret_cast<const float4*>(c->p_box_fast);
+    P.box_cull = reinterpret_cast<const float4*>(c->p_box_cull);
+    P.sph_hot = reinterpret_cast<const float4*>(c->p_sph);
+    P.obj_lrec = reinterpret_cast<const float4*>(c->p_obj_lrec);
+    P.box_obj = c->p_box_obj; P.sph_obj = c->p_sph_obj;
+    P.cold = c->p_cold; P.lights = c->p_lights;
+    P.counters = c->d_cnt.p;
+    P.n_box = c->n_box; P.n_sph = c->n_sph; P.n_lights = c->n_lights; P.max_depth = c->max_depth;
+    P.n_frames = n_frames; P.width = width; P.height = height; P.y0 = y0; P.y1 = y1;
+    P.spp = spp; P.seed = o.seed;
+    int n = 1;
+    while ((n + 1) * (n + 1) <= spp) n++;
+    P.spp_n = (n * n == spp) ? n : 0;
+    P.tiles_x = (width + 7) / 8; P.tiles_y = (band_rows + 3) / 4;
+    P.cull = 1; P.packet = 1; P.block = 1;              // this entry point IS the block kernel
+    P.fan = (o.no_cull & 32) ? 0 : 1;
+    {
+        static const float group_k = getenv("RT_GROUP_K") ? (float)atof(getenv("RT_GROUP_K")) : 0.01f;
+        static const float group_cos = getenv("RT_GROUP_COS") ? (float)atof(getenv("RT_GROUP_COS")) : 0.99f;
+        P.group_k = (o.no_cull & 64) ? 0.0f : group_k;
+        P.group_cos = group_cos;
+    }
+    P.extent = reinterpret_cast<const float*>(c->p_extent);
+    P.room_skip = 0;                                    // small-scene kernels only
+    P.n_lit = 0;                                        // packet tests: no per-light records
+    P.n_lit_batch = c->n_lit_total <= 3 ? c->n_lit_total : -1;
+    memcpy(P.lit, c->lit, sizeof(P.lit)); memcpy(P.amb_sum, c->amb_sum, sizeof(P.amb_sum));
+    memcpy(P.lit_pos, c->lit_pos, sizeof(P.lit_pos)); memcpy(P.lit_dif, c->lit_dif, sizeof(P.lit_dif));
+    memcpy(P.lit_spc, c->lit_spc, sizeof(P.lit_spc));
+    const size_t hot_bytes = ((size_t)P.n_box + P.n_sph) * 16;
+    P.resident = hot_bytes <= rt_fast::resident_limit_bytes(c->max_smem_optin, true) ? 1 : 0;
+    P.out = (uint8_t*)out_rgba_device;
+    P.frame_stride = band_only ? (long long)width * band_rows * 4 : (long long)width * height * 4;
+    P.out_row0 = band_only ? y0 : 0;
+
+    const char* why = "";
+    cudaError_t e = rt_fast::launch_block_noalloc(P, cams, c->device, c->sm_count, st, &why);
+    if (e == cudaErrorInvalidValue && why[0]) return fail(RT_ERR_UNSUPPORTED, "rt_render_block_noalloc: %s", why);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, "rt_render_block_noalloc: %s (%s)", cudaGetErrorString(e), why);
+    g_launches += 2;                                    // set-up kernel + render kernel
+    if (o.done_flag) {
+        if (rt_write_flag(reinterpret_cast<uint32_t*>(o.done_flag), o.done_value, st) != RT_OK)
+            return fail(RT_ERR_CUDA, "completion-flag launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        g_launches++;
+    }
+    if (st != c->stream) {
+        CU(cudaEventRecord(c->ev_render, st));
+        c->render_recorded = true;
+    }
+    if (!o.async) CU(cudaStreamSynchronize(st));
     return RT_OK;
 }
 
