@@ -303,9 +303,12 @@ def run_gpu(args, wl_name, wl):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     numa_cpus = None
+    numa_mem = None
     if world > 1:
         from openglraytracer_b200.multigpu import bind_to_gpu_numa
         numa_cpus = bind_to_gpu_numa(local)         # before any page-locked allocation
+        from openglraytracer_b200.multigpu import prefer_gpu_numa_memory
+        numa_mem = prefer_gpu_numa_memory(local) if not os.environ.get("RT_NO_NUMA_MEMORY") else None
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
@@ -586,7 +589,9 @@ def run_gpu(args, wl_name, wl):
                              "value_traversed only those the kernel traverses: shadow rays toward a light without diffuse / "
                              "specular terms, or from a surface whose Phong weight is 0, cannot change the pixel and are skipped"},
             "kernel": "fast (fmad on, no fast-math); kernel sources " + csrc_sha(),
-            "host_binding": ("each rank on the %d cores next to its GPU (NVML affinity)" % len(numa_cpus)) if numa_cpus else "launcher default",
+            "host_binding": (("each rank on the %d cores NVML names for its GPU" % len(numa_cpus)) if numa_cpus else "launcher default") +
+                            ("; page-locked frames preferred on the GPU's NUMA node (rank 0: node %d)" % numa_mem if numa_mem is not None
+                             else "; memory policy unchanged (one node, unknown topology or set_mempolicy refused)"),
             "e2e": {"value": e2e_value, "value_traversed": e2e_trav, "unit": UNIT, "h2d_bytes_per_step": scene_bytes,
                     "d2h_bytes_per_step": nfr * w * h * 4, "steps": e2e_steps, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "checksum": checksum},

@@ -35,6 +35,44 @@ def bind_to_gpu_numa(device_index):
         return None
 
 
+def gpu_numa_node(device_index):
+    """NUMA node the GPU's PCIe slot hangs off (sysfs), or None."""
+    try:
+        props = torch.cuda.get_device_properties(int(device_index))
+        bus = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
+            node = int(f.read().strip())
+        return node if node >= 0 else None
+    except Exception:        # noqa: BLE001 - attribute / file missing: unknown topology
+        return None
+
+
+def prefer_gpu_numa_memory(device_index):
+    """Page-locked frames of this process on the GPU's OWN NUMA node: set_mempolicy(MPOL_PREFERRED, node) before the
+    frames are allocated.  The CPU affinity NVML reports can be one mask for every GPU (a container's cpuset on one
+    socket): the processes then all allocate on that socket, and the posted PCIe frame stores of the GPUs behind the
+    other socket cross the socket interconnect.  Memory policy is independent of where the threads run.  Best effort:
+    returns the node, or None (unknown topology, single node, or the sandbox refuses the system call)."""
+    import ctypes
+    node = gpu_numa_node(device_index)
+    if node is None or not os.path.isdir("/sys/devices/system/node/node%d" % node):
+        return None
+    try:
+        n_nodes = len([d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()])
+        if n_nodes < 2:
+            return None
+        libc = ctypes.CDLL(None, use_errno=True)
+        mask = (ctypes.c_ulong * 16)()
+        mask[node // 64] = 1 << (node % 64)
+        MPOL_PREFERRED, SYS_set_mempolicy = 1, 238          # x86_64
+        if os.uname().machine != "x86_64":
+            return None
+        rc = libc.syscall(SYS_set_mempolicy, MPOL_PREFERRED, mask, ctypes.c_ulong(16 * 64))
+        return node if rc == 0 else None
+    except Exception:        # noqa: BLE001
+        return None
+
+
 def row_band(rank, world, height):
     """Contiguous band [y0, y1) of rank `rank`: rows g*H/G .. (g+1)*H/G."""
     return (rank * height) // world, ((rank + 1) * height) // world
