@@ -1498,6 +1498,33 @@ __device__ __forceinline__ void shade_small(const RtParams& P, const WarpCtx& w,
     }
 }
 
+// -------------------------------------------------------------------------
+// Phong terms with explicit roundings (madd / __fmul_rn / __fadd_rn): trace_sample and trace_sample3 evaluate the
+// same pixels along different code paths and must agree bit for bit, so nothing here is left to the compiler's
+// FMA contraction (which is chosen per inlined instance).
+// -------------------------------------------------------------------------
+// diffuse += L.diffuse * M.diffuse * max(n.l, 0); specular += L.specular * M.specular * pow(max(v.r, 0), shininess)  (glsl:822-833)
+__device__ __forceinline__ void phong_light(const RtLightDev* __restrict__ L, const RtCold* __restrict__ mat, V3 sd, V3 n, V3 view,
+                                            float (&dif)[4], float (&spc)[4]) {
+    const V3 light_dir = normalize3(sd);                                     // glsl:804
+    const V3 light_ref = normalize3(reflect3(-light_dir, n));                // glsl:825
+    const float kd = fmaxf(dot3(light_dir, n), 0.0f);                        // glsl:826
+    const float ks = fpow(fmaxf(dot3(view, light_ref), 0.0f), mat->shininess);   // glsl:827, 832
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        dif[k] = madd(__fmul_rn(L->diffuse[k], mat->diffuse[k]), kd, dif[k]);        // glsl:830
+        spc[k] = madd(__fmul_rn(L->specular[k], mat->specular[k]), ks, spc[k]);      // glsl:832
+    }
+}
+// (ambient + diffuse + specular + emissive).rgb * .a  (glsl:837-839), added to the pixel with the node's weight
+__device__ __forceinline__ V3 phong_accumulate(V3 color, float wp, const float (&amb)[4], const float (&dif)[4], const float (&spc)[4],
+                                               const RtCold* __restrict__ mat) {
+    float pc[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) pc[k] = __fadd_rn(__fadd_rn(__fadd_rn(amb[k], dif[k]), spc[k]), mat->emissive[k]);
+    return mk(madd(wp, __fmul_rn(pc[0], pc[3]), color.x), madd(wp, __fmul_rn(pc[1], pc[3]), color.y), madd(wp, __fmul_rn(pc[2], pc[3]), color.z));
+}
+
 // Pending rays of one lane: origin, direction, weight, remaining depth.  BOUNCE = false (MAX_RAYTRACE_DEPTH = 0,
 // the shader as shipped, glsl:22): the tree is its root, there is nothing to keep -- no local-memory frame at all.
 template <bool BOUNCE> struct RayStack;
@@ -1636,7 +1663,7 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                 for (int l = 0; l < P.n_lights; ++l) {
                     if (shade) {
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) amb[k] += P.lights[l].ambient[k] * mat->ambient[k];
+                        for (int k = 0; k < 4; ++k) amb[k] = madd(P.lights[l].ambient[k], mat->ambient[k], amb[k]);
                         if (COUNT) { cnt.rays++; cnt.shadow_rays++; }
                     }
                 }
@@ -1736,29 +1763,14 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
                 for (int r = 0; r < kShadowBatch; ++r) {
                     if (shade && r < n_slots && !(sb[r] < 1.0f)) {
                         if (COUNT) cnt.shaded_lights++;
-                        const RtLightDev* __restrict__ L = P.lights + li[r];
-                        const V3 light_dir = normalize3(sd[r]);                                  // glsl:804
-                        const V3 light_ref = normalize3(reflect3(-light_dir, h.n));              // glsl:825
-                        const float cos_theta = dot3(light_dir, h.n);                            // glsl:826
-                        const float cos_phi = dot3(view, light_ref);                             // glsl:827
-                        const float kd = fmaxf(cos_theta, 0.0f);
-                        const float ks = fpow(fmaxf(cos_phi, 0.0f), mat->shininess);             // glsl:832
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            dif[k] += L->diffuse[k] * mat->diffuse[k] * kd;                      // glsl:830
-                            spc[k] += L->specular[k] * mat->specular[k] * ks;                    // glsl:832
-                        }
+                        phong_light(P.lights + li[r], mat, sd[r], h.n, view, dif, spc);
                     }
                 }
             }
         }   // general path
         }
         if (hit) {
-            float pc[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) pc[k] = ((amb[k] + dif[k]) + spc[k]) + mat->emissive[k];    // glsl:837
-            const V3 phong = mk(pc[0] * pc[3], pc[1] * pc[3], pc[2] * pc[3]);                        // glsl:839
-            if (shade) color = color + wp * phong;
+            if (shade) color = phong_accumulate(color, wp, amb, dif, spc, mat);                     // glsl:837-839
             // PHASES 2-3: each child ray is pushed with its product weight
             if (refracted) {                                                                        // glsl:1010-1027
                 const V3 ro = axpy3(h.n, -0.001f, h.p);
@@ -1777,6 +1789,282 @@ __device__ __forceinline__ V3 trace_sample(const RtParams& P, WarpCtx& w, bool v
     }
     if (iters >= 10001) { if (COUNT) cnt.red_pixels++; return mk(1.0f, 0.0f, 0.0f); }
     return color;
+}
+
+// -------------------------------------------------------------------------
+// recursive_raytrace (glsl:1071-1105) for the THREE samples of a lane (one per 8x4 tile of the work item) in
+// lockstep: large scenes with bounce rays.  trace_sample() runs the three bounce trees of a lane one after the
+// other, so a grouping round sees 32 rays; here every iteration pops one pending ray per (lane, tile) -- up to 96 --
+// and groups them across lanes AND tiles, for the closest-hit packets (secondary_packets' rule: direction within
+// P.group_cos of a leader's, origin within sqrt(rg2) of it) and, light by light, for the shadow packets of the hit
+// points (one cone from the light around a group of hit points, as the root phase does).  Every pass still scans
+// all N objects; there are about half as many passes per ray.  Per-ray loops take what the groups leave over.
+// Same nodes in the same per-pixel order, same exact tests (candidate_test is order-independent), same shading
+// arithmetic (phong_light / phong_accumulate) as trace_sample: frames are byte-identical (no_cull bit 6).
+// -------------------------------------------------------------------------
+constexpr int kMaxGroups3 = 20;
+template <bool SMEM, bool COUNT>
+__device__ __forceinline__ void trace_sample3(const RtParams& P, WarpCtx& w, const bool (&valid)[kShadowBatch], V3 org,
+                                              const V3 (&dir)[kShadowBatch], const float (&first_t)[kShadowBatch],
+                                              const int (&first_idx)[kShadowBatch], bool have_sb,
+                                              const float (&first_sb)[kShadowBatch][kShadowBatch], float pk_pad1, float pk_pad2,
+                                              RtCounters& cnt, V3 (&color)[kShadowBatch]) {
+    constexpr int Q = kShadowBatch;
+    constexpr bool REPACK = true, CULL = true;
+    RayStack<true> stack[Q];
+    int iters[Q];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) { stack[q].init(valid[q], org, dir[q], P.max_depth); color[q] = mk(0.0f, 0.0f, 0.0f); iters[q] = 0; }
+    const float rg2 = pk_pad2 * 2.5e5f * P.group_k;
+    const int n_lit = P.n_lit_batch;                      // 0..3 (checked by the caller)
+    bool first_now = true;
+
+    while (__any_sync(kFull, stack[0].pending() || stack[1].pending() || stack[2].pending())) {
+        bool act[Q];
+        V3 o[Q], d[Q];
+        float wgt[Q], best[Q];
+        int depth[Q], bidx[Q];
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+            act[q] = stack[q].pending();
+            wgt[q] = 0.0f; depth[q] = 0; bidx[q] = -1;
+            if (act[q]) { stack[q].pop(o[q], d[q], wgt[q], depth[q]); best[q] = kFar; }
+            else { o[q] = mk(0.0f, 0.0f, 0.0f); d[q] = mk(0.0f, 0.0f, 1.0f); best[q] = 0.0f; }
+        }
+        // ---- PHASE 0 (glsl:956-967): closest hits
+        if (first_now) {                                  // the root rays were traced by the caller
+#pragma unroll
+            for (int q = 0; q < Q; ++q) if (act[q]) { best[q] = first_t[q]; bidx[q] = first_idx[q]; }
+        } else {
+            bool todo[Q];
+            V3 u[Q];
+#pragma unroll
+            for (int q = 0; q < Q; ++q) {
+                const float l2 = dot3(d[q], d[q]);
+                todo[q] = act[q] && l2 > 0.0f && l2 < 1e30f;        // zero / NaN direction (refract()'s TIR): misses everything
+                u[q] = d[q] * rsqrtf(l2);
+            }
+            for (int round = 0; round < kMaxGroups3; ++round) {
+                const unsigned r0 = __ballot_sync(kFull, todo[0]), r1 = __ballot_sync(kFull, todo[1]), r2 = __ballot_sync(kFull, todo[2]);
+                if ((r0 | r1 | r2) == 0u) break;
+                const int ql = r0 ? 0 : (r1 ? 1 : 2);                  // the leader: first pending (tile, lane)
+                const int lead = __ffs(r0 ? r0 : (r1 ? r1 : r2)) - 1;
+                const V3 us = ql == 0 ? u[0] : (ql == 1 ? u[1] : u[2]);
+                const V3 os = ql == 0 ? o[0] : (ql == 1 ? o[1] : o[2]);
+                const V3 lu = mk(__shfl_sync(kFull, us.x, lead), __shfl_sync(kFull, us.y, lead), __shfl_sync(kFull, us.z, lead));
+                const V3 lo = mk(__shfl_sync(kFull, os.x, lead), __shfl_sync(kFull, os.y, lead), __shfl_sync(kFull, os.z, lead));
+                bool in_g[Q];
+                float acc[7] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    const V3 dl = o[q] - lo;
+                    in_g[q] = todo[q] && ((q == ql && w.lane == lead) || (dot3(u[q], lu) >= P.group_cos && dot3(dl, dl) <= rg2));
+                    if (in_g[q]) { acc[0] += u[q].x; acc[1] += u[q].y; acc[2] += u[q].z; acc[3] += o[q].x; acc[4] += o[q].y; acc[5] += o[q].z; acc[6] += 1.0f; }
+                }
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+                    for (int c = 0; c < 7; ++c) acc[c] += __shfl_xor_sync(kFull, acc[c], off);
+                }
+                Cone gc[1];
+                const float inv_n = 1.0f / acc[6];
+                gc[0].apex = mk(acc[3] * inv_n, acc[4] * inv_n, acc[5] * inv_n);
+                gc[0].axis = normalize3(mk(acc[0], acc[1], acc[2]));
+                float s2 = 0.0f, ro2 = 0.0f;
+                unsigned want = 0u;
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    const V3 x = cross3(gc[0].axis, u[q]);
+                    const V3 da = o[q] - gc[0].apex;
+                    if (in_g[q]) {
+                        s2 = fmaxf(s2, fminf(__fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z))), 1.0f));
+                        ro2 = fmaxf(ro2, dot3(da, da));
+                    }
+                    if (__any_sync(kFull, in_g[q])) want |= 1u << q;
+                }
+                cone_close(gc[0], warp_max_nonneg(s2), 1e18f);
+                const float grow = __fmaf_rn(sqrt_approx(warp_max_nonneg(ro2)), 1.001f, pk_pad1);
+                float b3[Q]; int i3[Q];
+#pragma unroll
+                for (int q = 0; q < Q; ++q) { b3[q] = in_g[q] ? kFar : 0.0f; i3[q] = -1; }
+                packet_trace<SMEM, COUNT, 1>(P, w, gc, 1u, grow, 1e-45f, pk_pad1, pk_pad2, false, o, d, b3, i3, cnt, want);
+                if (COUNT && w.lane == 0) cnt.group_passes++;
+#pragma unroll
+                for (int q = 0; q < Q; ++q) if (in_g[q]) { best[q] = b3[q]; bidx[q] = i3[q]; todo[q] = false; }
+            }
+#pragma unroll 1
+            for (int q = 0; q < Q; ++q) {                             // what the groups left over: per-ray loops
+                const bool tq = q == 0 ? todo[0] : (q == 1 ? todo[1] : todo[2]);
+                if (!__any_sync(kFull, tq)) continue;
+                const V3 oq = q == 0 ? o[0] : (q == 1 ? o[1] : o[2]), dq = q == 0 ? d[0] : (q == 1 ? d[1] : d[2]);
+                float b1 = tq ? kFar : 0.0f; int i1 = -1;
+                if (COUNT && w.lane == 0) cnt.loop_passes++;
+                trace_closest<SMEM, REPACK, COUNT, CULL>(P, w, oq, dq, b1, i1, cnt);
+                if (tq) { if (q == 0) { best[0] = b1; bidx[0] = i1; } else if (q == 1) { best[1] = b1; bidx[1] = i1; } else { best[2] = b1; bidx[2] = i1; } }
+            }
+        }
+        // ---- hit records, bounce weights (glsl:979-1054: final = mix(mix(phong, refl, kr), refr, kt) is linear)
+        V3 hp[Q], hn[Q], so[Q], view[Q];
+        float wp[Q], wr[Q], wt[Q], ratio[Q];
+        int obj[Q];
+        bool shade[Q], reflected[Q], refracted[Q], hit[Q];
+#pragma unroll 1
+        for (int q = 0; q < Q; ++q) {
+            hit[q] = act[q] && bidx[q] >= 0;
+            if (COUNT && act[q]) { cnt.rays++; cnt.nodes++; cnt.hit_nodes += hit[q]; }
+            if (act[q]) iters[q] += hit[q] ? 6 : 1;
+            hp[q] = hn[q] = so[q] = view[q] = mk(0.0f, 0.0f, 0.0f);
+            wp[q] = wr[q] = wt[q] = ratio[q] = 0.0f; obj[q] = 0;
+            shade[q] = reflected[q] = refracted[q] = false;
+            if (hit[q]) {
+                const Hit h = resolve_hit<SMEM, CULL>(P, w, o[q], d[q], best[q], bidx[q]);
+                const RtCold* __restrict__ mat = P.cold + h.obj;
+                const float kr = mat->reflectivity, kt = mat->transparency;
+                reflected[q] = depth[q] > 0 && kr > 0.0f;
+                refracted[q] = depth[q] > 0 && kt > 0.0f;
+                float a = wgt[q], b = wgt[q] * kr;
+                if (reflected[q]) a = a * (1.0f - kr);
+                if (refracted[q]) { a = a * (1.0f - kt); b = b * (1.0f - kt); }
+                wp[q] = a; wr[q] = b; wt[q] = wgt[q] * kt;
+                ratio[q] = h.inside ? mat->ior_back : mat->inv_ior;
+                hp[q] = h.p; hn[q] = h.n; obj[q] = h.obj;
+                shade[q] = a != 0.0f;
+                if (COUNT && !shade[q]) { cnt.rays += P.n_lights; cnt.shadow_rays += P.n_lights; cnt.pad += P.n_lights; }
+                if (COUNT && shade[q]) { cnt.rays += P.n_lights; cnt.shadow_rays += P.n_lights; cnt.pad += P.n_lights - n_lit; }
+                if (shade[q]) { view[q] = normalize3(-d[q]); so[q] = axpy3(h.n, 0.01f, h.p); }       // glsl:827, 808
+            }
+        }
+        if (COUNT) cnt.warp_iters += Q;
+
+        // ---- PHASE 1: shadow rays (glsl:807-819), light by light: sb[q][k] < 1 iff occluded
+        float sb[Q][kShadowBatch];
+        bool left[Q] = {false, false, false};
+#pragma unroll
+        for (int q = 0; q < Q; ++q)
+#pragma unroll
+            for (int k = 0; k < kShadowBatch; ++k) sb[q][k] = (shade[q] && k < n_lit) ? ((first_now && have_sb) ? first_sb[q][k] : 1.0f) : 0.0f;
+        if (!(first_now && have_sb) && __any_sync(kFull, shade[0] || shade[1] || shade[2])) {
+#pragma unroll 1
+            for (int k = 0; k < n_lit; ++k) {
+                const RtLightDev* __restrict__ L = P.lights + P.lit[k];
+                const V3 lp = mk(L->position[0], L->position[1], L->position[2]);
+                V3 sd3[Q], uu[Q];
+                float ll[Q], sbk[Q];
+                bool todo[Q];
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    sd3[q] = shade[q] ? mk(lp.x - hp[q].x, lp.y - hp[q].y, lp.z - hp[q].z) : mk(0.0f, 0.0f, 1.0f);      // glsl:809
+                    ll[q] = __fmaf_rn(sd3[q].x, sd3[q].x, __fmaf_rn(sd3[q].y, sd3[q].y, __fmul_rn(sd3[q].z, sd3[q].z)));
+                    uu[q] = sd3[q] * -rsqrtf(ll[q]);                  // from the light toward the hit point
+                    todo[q] = shade[q];
+                    sbk[q] = shade[q] ? 1.0f : 0.0f;
+                }
+                for (int round = 0; round < kMaxGroups3; ++round) {
+                    const unsigned r0 = __ballot_sync(kFull, todo[0]), r1 = __ballot_sync(kFull, todo[1]), r2 = __ballot_sync(kFull, todo[2]);
+                    if ((r0 | r1 | r2) == 0u) break;
+                    bool in_g[Q] = {todo[0], todo[1], todo[2]};       // round 0: every hit point of the work item
+                    if (round > 0) {                                  // then neighbours of a leader
+                        const int ql = r0 ? 0 : (r1 ? 1 : 2);
+                        const int lead = __ffs(r0 ? r0 : (r1 ? r1 : r2)) - 1;
+                        const V3 ps = ql == 0 ? hp[0] : (ql == 1 ? hp[1] : hp[2]);
+                        const V3 lh = mk(__shfl_sync(kFull, ps.x, lead), __shfl_sync(kFull, ps.y, lead), __shfl_sync(kFull, ps.z, lead));
+#pragma unroll
+                        for (int q = 0; q < Q; ++q) {
+                            const V3 dl = hp[q] - lh;
+                            in_g[q] = todo[q] && ((q == ql && w.lane == lead) || dot3(dl, dl) <= rg2);
+                        }
+                    }
+                    V3 sm = mk(0.0f, 0.0f, 0.0f);
+#pragma unroll
+                    for (int q = 0; q < Q; ++q) if (in_g[q]) sm = sm + uu[q];
+#pragma unroll
+                    for (int off = 16; off > 0; off >>= 1) {
+                        sm.x += __shfl_xor_sync(kFull, sm.x, off);
+                        sm.y += __shfl_xor_sync(kFull, sm.y, off);
+                        sm.z += __shfl_xor_sync(kFull, sm.z, off);
+                    }
+                    Cone lc[1];
+                    lc[0].apex = lp;
+                    lc[0].axis = normalize3(sm);
+                    float s2 = 0.0f, lmax = 0.0f;
+                    bool in_cone = true;
+                    unsigned want = 0u;
+#pragma unroll
+                    for (int q = 0; q < Q; ++q) {
+                        const V3 x = cross3(lc[0].axis, uu[q]);
+                        if (in_g[q]) {
+                            s2 = fmaxf(s2, fminf(__fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z))), 1.0f));
+                            lmax = fmaxf(lmax, ll[q]);
+                            in_cone = in_cone && dot3(lc[0].axis, uu[q]) >= kConeMinCos;            // NaN -> false
+                        }
+                        if (__any_sync(kFull, in_g[q])) want |= 1u << q;
+                    }
+                    if (__all_sync(kFull, in_cone)) {
+                        cone_close(lc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
+                        float sbg[Q]; int unused[Q] = {-1, -1, -1};
+#pragma unroll
+                        for (int q = 0; q < Q; ++q) sbg[q] = in_g[q] ? 1.0f : 0.0f;
+                        packet_trace<SMEM, COUNT, 1>(P, w, lc, 1u, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so, sd3, sbg, unused, cnt, want);
+                        if (COUNT && w.lane == 0 && round > 0) cnt.shadow_group_passes++;
+#pragma unroll
+                        for (int q = 0; q < Q; ++q) if (in_g[q]) { sbk[q] = sbg[q]; todo[q] = false; }
+                    } else if (round > 0) {                           // this neighbourhood is too wide seen from the light
+#pragma unroll
+                        for (int q = 0; q < Q; ++q) if (in_g[q]) { left[q] = true; todo[q] = false; }
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    left[q] = left[q] || todo[q];
+                    if (k == 0) sb[q][0] = sbk[q]; else if (k == 1) sb[q][1] = sbk[q]; else sb[q][2] = sbk[q];
+                }
+            }
+#pragma unroll 1
+            for (int q = 0; q < Q; ++q) {                             // leftovers: the per-ray loops, all lights of the hit point
+                const bool lq = q == 0 ? left[0] : (q == 1 ? left[1] : left[2]);
+                if (!__any_sync(kFull, lq)) continue;
+                if (COUNT && w.lane == 0) cnt.loop_passes++;
+                V3 sdq[kShadowBatch]; float sbq[kShadowBatch];
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) {
+                    const RtLightDev* __restrict__ L = P.lights + P.lit[k < n_lit ? k : 0];
+                    const bool on = shade[q] && k < n_lit;
+                    sdq[k] = on ? mk(L->position[0] - hp[q].x, L->position[1] - hp[q].y, L->position[2] - hp[q].z) : mk(0.0f, 0.0f, 1.0f);
+                    sbq[k] = on ? 1.0f : 0.0f;
+                }
+                trace_shadow<SMEM, REPACK, COUNT, CULL, false>(P, w, so[q], sdq, sbq, n_lit, cnt);
+#pragma unroll
+                for (int k = 0; k < kShadowBatch; ++k) if (shade[q] && k < n_lit) sb[q][k] = sbq[k];      // same outcome for rays traced before
+            }
+        }
+
+        // ---- shading (glsl:789-840) and PHASES 2-3: each child ray is pushed with its product weight
+#pragma unroll 1
+        for (int q = 0; q < Q; ++q) {
+            if (hit[q]) {
+                const RtCold* __restrict__ mat = P.cold + obj[q];
+                if (shade[q]) {
+                    float amb[4], dif[4] = {0, 0, 0, 0}, spc[4] = {0, 0, 0, 0};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) amb[k] = P.amb_sum[k] * mat->ambient[k];
+                    for (int k = 0; k < n_lit; ++k) {
+                        if (!(sb[q][k] < 1.0f)) {
+                            if (COUNT) cnt.shaded_lights++;
+                            const RtLightDev* __restrict__ L = P.lights + P.lit[k];
+                            phong_light(L, mat, mk(L->position[0] - hp[q].x, L->position[1] - hp[q].y, L->position[2] - hp[q].z), hn[q], view[q], dif, spc);
+                        }
+                    }
+                    color[q] = phong_accumulate(color[q], wp[q], amb, dif, spc, mat);
+                }
+                if (refracted[q]) stack[q].push(axpy3(hn[q], -0.001f, hp[q]), refract3(d[q], hn[q], ratio[q]), wt[q], depth[q] - 1);   // glsl:1010-1027
+                if (reflected[q]) stack[q].push(axpy3(hn[q], 0.001f, hp[q]), reflect3(d[q], hn[q]), wr[q], depth[q] - 1);              // glsl:988-994
+            }
+            if (iters[q] >= 10001) stack[q].clear();                  // runaway guard (glsl:1076-1101)
+        }
+        first_now = false;
+    }
+#pragma unroll
+    for (int q = 0; q < Q; ++q) if (iters[q] >= 10001) { if (COUNT) cnt.red_pixels++; color[q] = mk(1.0f, 0.0f, 0.0f); }
 }
 
 // -------------------------------------------------------------------------
@@ -2012,9 +2300,21 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
                         }
                     }
                 }
+                // bounce rays of a large scene: the three trees of a lane in lockstep, rays grouped over all 96 (trace_sample3)
+                bool lockstep = false;
+                if constexpr (BOUNCE && CULL && REPACK && !RT_STRICT) {
+                    lockstep = P.packet && P.group_k > 0.0f && P.n_lit_batch >= 0;       // warp-uniform
+                    if (lockstep) {
+                        const bool v3[kShadowBatch] = {valid[0], valid[NP > 1 ? 1 : 0], valid[NP > 2 ? 2 : 0]};
+                        V3 c3[kShadowBatch];
+                        trace_sample3<SMEM, COUNT>(P, w, v3, org, dir, best, bidx, have_sb, rsb, pk_pad1, pk_pad2, cnt, c3);
+#pragma unroll
+                        for (int q = 0; q < NP; ++q) sum[q] = sum[q] + c3[q];
+                    }
+                }
                 // one copy of the bounce machinery in the instruction stream: rolled loop, selected operands
 #pragma unroll 1
-                for (int q = 0; q < NP; ++q) {
+                for (int q = 0; q < (lockstep ? 0 : NP); ++q) {
                     const V3 dq = q == 0 ? dir[0] : (q == 1 ? dir[1] : dir[2]);
                     const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
                     const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);

@@ -500,9 +500,20 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     }
                 }
             }
+            // bounce rays: the three trees of a lane in lockstep, rays grouped over all 96 (trace_sample3)
+            bool lockstep = false;
+            if constexpr (BOUNCE) {
+                lockstep = P.group_k > 0.0f && P.n_lit_batch >= 0;                        // CTA-uniform
+                if (lockstep) {
+                    V3 c3[kShadowBatch];
+                    trace_sample3<SMEM, COUNT>(P, w, valid, org, dir, best, bidx, have_sb, rsb, pk_pad1, pk_pad2, cnt, c3);
+#pragma unroll
+                    for (int q = 0; q < NP; ++q) sum[q] = sum[q] + c3[q];
+                }
+            }
             // one copy of the bounce machinery in the instruction stream: rolled loop, selected operands
 #pragma unroll 1
-            for (int q = 0; q < NP; ++q) {
+            for (int q = 0; q < (lockstep ? 0 : NP); ++q) {
                 const V3 dq = q == 0 ? dir[0] : (q == 1 ? dir[1] : dir[2]);
                 const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
                 const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
