@@ -158,7 +158,7 @@ typedef struct rt_options {
 
 /* Environment variables (read once per process; profiling / tuning aids, results are byte-identical whatever they
  * say):  RT_GROUP_K    bounce rays as grouped packets: (group radius / scene extent)^2, default 0.01
- *        RT_GROUP_COS  ... and the cosine of the largest angle between a group member and its leader, default 0.99
+ *        RT_GROUP_COS  ... and the cosine of the largest angle between a group member and its leader, default 0.94
  *        RT_BLOCK_LOG  path: the instrumented twin of the block kernel (rt_options.stats != NULL) dumps one 64-byte
  *                      timing record per block of 48 x 16 pixels there (tools/block_log.py) */
 #define RT_HOST_STORE_AUTO   0

@@ -561,8 +561,12 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         cams[k].position[2] = cam.position[2]; cams[k].position[3] = 1.0f;
     }
     if (o.stats) CU(cudaEventRecord(c->ev[2], st));
-    CU(c->d_cams.reserve(n_frames));
-    CU(cudaMemcpyAsync(c->d_cams.p, cams.data(), sizeof(RtCameraDev) * n_frames, cudaMemcpyHostToDevice, st));
+    // one frame: the 80 bytes of camera uniforms ride in the kernel parameters (no copy); a batch goes up as an array
+    const bool cam_inline = n_frames == 1;
+    if (!cam_inline) {
+        CU(c->d_cams.reserve(n_frames));
+        CU(cudaMemcpyAsync(c->d_cams.p, cams.data(), sizeof(RtCameraDev) * n_frames, cudaMemcpyHostToDevice, st));
+    }
 
     const int band_rows = y1 - y0;
     const bool band_only = o.out_band_only != 0;
@@ -576,7 +580,8 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     P.sph_hot = reinterpret_cast<const float4*>(c->p_sph);
     P.obj_lrec = reinterpret_cast<const float4*>(c->p_obj_lrec);
     P.box_obj = c->p_box_obj; P.sph_obj = c->p_sph_obj;
-    P.cold = c->p_cold; P.lights = c->p_lights; P.cams = c->d_cams.p;
+    P.cold = c->p_cold; P.lights = c->p_lights; P.cams = cam_inline ? nullptr : c->d_cams.p;
+    if (cam_inline) P.cam0 = cams[0];
     P.counters = c->d_cnt.p;
     P.tile_counter = c->d_tile.p;
     P.n_box = c->n_box; P.n_sph = c->n_sph; P.n_lights = c->n_lights; P.max_depth = c->max_depth;
@@ -601,7 +606,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     {
         // tuning knobs, read once: RT_GROUP_K (group radius^2 / E^2), RT_GROUP_COS (direction spread of a group)
         static const float group_k = getenv("RT_GROUP_K") ? (float)atof(getenv("RT_GROUP_K")) : 0.01f;
-        static const float group_cos = getenv("RT_GROUP_COS") ? (float)atof(getenv("RT_GROUP_COS")) : 0.99f;
+        static const float group_cos = getenv("RT_GROUP_COS") ? (float)atof(getenv("RT_GROUP_COS")) : 0.94f;
         P.group_k = (P.packet && !(o.no_cull & 64)) ? group_k : 0.0f;
         P.group_cos = group_cos;
     }
@@ -792,7 +797,7 @@ int rt_render_block_noalloc(rt_context* c, const rt_camera* cameras, int n_frame
     P.fan = (o.no_cull & 32) ? 0 : 1;
     {
         static const float group_k = getenv("RT_GROUP_K") ? (float)atof(getenv("RT_GROUP_K")) : 0.01f;
-        static const float group_cos = getenv("RT_GROUP_COS") ? (float)atof(getenv("RT_GROUP_COS")) : 0.99f;
+        static const float group_cos = getenv("RT_GROUP_COS") ? (float)atof(getenv("RT_GROUP_COS")) : 0.94f;
         P.group_k = (o.no_cull & 64) ? 0.0f : group_k;
         P.group_cos = group_cos;
     }

@@ -2158,7 +2158,7 @@ __global__ void __launch_bounds__(kThreads, REPACK ? (CULL ? RT_MIN_BLOCKS_CULL 
             px[q] = (tx * NP + q) * 8 + lx;
             valid[q] = px[q] < P.width && py < P.y1;
         }
-        const RtCameraDev* __restrict__ cam = P.cams + frame;
+        const RtCameraDev* __restrict__ cam = P.cams ? P.cams + frame : &P.cam0;
         const V3 org = mk(cam->position[0], cam->position[1], cam->position[2]);   // glsl:391
 
         V3 sum[NP];

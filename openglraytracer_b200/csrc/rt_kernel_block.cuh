@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
             px[q] = (tx * NP + q) * 8 + lx;
             valid[q] = item_ok && px[q] < P.width && py < P.y1;
         }
-        const RtCameraDev* __restrict__ cam = P.cams + frame;
+        const RtCameraDev* __restrict__ cam = P.cams ? P.cams + frame : &P.cam0;
         const V3 org = mk(cam->position[0], cam->position[1], cam->position[2]);   // glsl:391
 
         // ---- the block's primary cone: axis through the middle of its 48 x 16 pixels, half-angle from its corner
@@ -340,6 +340,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 };
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
+                    thr[k] = 0.0f;
+                    if (k >= n_lights_b) continue;                     // CTA-uniform: no such lit light (the built-in lights: two)
                     float dsum = 0.0f, dn = 0.0f;
                     V3 u[kShadowBatch]; float l2[kShadowBatch];
 #pragma unroll
@@ -374,6 +376,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 unsigned on = 0u;
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
+                    lc[k].apex = lp[k]; lc[k].axis = mk(0.0f, 0.0f, 1.0f);
+                    if (k >= n_lights_b) continue;                     // unused slot: its `on` bit stays off
                     float t4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
                     for (int ww = 0; ww < kWarps; ++ww) {
 #pragma unroll
@@ -411,6 +415,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 float ball[kShadowBatch];
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) {
+                    if (k >= n_lights_b) { cone_close(lc[k], 0.0f, 0.0f); ball[k] = 0.0f; continue; }
                     float s2 = 0.0f, lmax = 0.0f, nmax = 0.0f, hmax = 0.0f;
                     bool k_ok = true;
                     for (int ww = 0; ww < kWarps; ++ww) {
