@@ -290,12 +290,16 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
             // ---- root hits: hit point, shadow-ray origin and "needs shading" exactly as trace_sample builds them
             bool have_sb = false;
             float rsb[kShadowBatch][kShadowBatch];       // [tile q][light slot]
+            V3 hp[kShadowBatch], hn3[kShadowBatch];      // hit point and shading normal of the three root hits
+            int ob3[kShadowBatch];                       // their objects' original indices (-1: no hit)
+#pragma unroll
+            for (int q = 0; q < kShadowBatch; ++q) { hp[q] = mk(0.0f, 0.0f, 0.0f); hn3[q] = mk(0.0f, 0.0f, 1.0f); ob3[q] = -1; }
 #pragma unroll
             for (int q = 0; q < kShadowBatch; ++q)
 #pragma unroll
                 for (int k = 0; k < kShadowBatch; ++k) rsb[q][k] = 0.0f;
             if (n_lights_b > 0) {                        // CTA-uniform
-                V3 hp[kShadowBatch], so3[kShadowBatch];
+                V3 so3[kShadowBatch];
                 bool sh[kShadowBatch];
 #pragma unroll 1
                 for (int q = 0; q < kShadowBatch; ++q) {
@@ -304,7 +308,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
                     const bool vq = q == 0 ? valid[0] : (q == 1 ? valid[1] : valid[2]);
                     bool shade = false;
-                    V3 p = mk(0.0f, 0.0f, 0.0f), so = mk(0.0f, 0.0f, 0.0f);
+                    V3 p = mk(0.0f, 0.0f, 0.0f), so = mk(0.0f, 0.0f, 0.0f), nn = mk(0.0f, 0.0f, 1.0f);
+                    int ob = -1;
                     if (vq && iq >= 0) {
                         const Hit h = resolve_hit<SMEM, CULL>(P, w, org, dq, tq, iq);
                         const RtCold* __restrict__ mat = P.cold + h.obj;
@@ -312,12 +317,12 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                         if (P.max_depth > 0 && mat->reflectivity > 0.0f) wp = wp * (1.0f - mat->reflectivity);
                         if (P.max_depth > 0 && mat->transparency > 0.0f) wp = wp * (1.0f - mat->transparency);
                         shade = wp != 0.0f;
-                        p = h.p;
+                        p = h.p; nn = h.n; ob = h.obj;
                         so = axpy3(h.n, 0.01f, h.p);                                            // glsl:808
                     }
-                    if (q == 0) { hp[0] = p; so3[0] = so; sh[0] = shade; }
-                    else if (q == 1) { hp[1] = p; so3[1] = so; sh[1] = shade; }
-                    else { hp[2] = p; so3[2] = so; sh[2] = shade; }
+                    if (q == 0) { hp[0] = p; hn3[0] = nn; ob3[0] = ob; so3[0] = so; sh[0] = shade; }
+                    else if (q == 1) { hp[1] = p; hn3[1] = nn; ob3[1] = ob; so3[1] = so; sh[1] = shade; }
+                    else { hp[2] = p; hn3[2] = nn; ob3[2] = ob; so3[2] = so; sh[2] = shade; }
                 }
                 // ---- the block's light cones: sum of the unit directions light -> hit point over the CTA ...
                 V3 lp[kShadowBatch];
@@ -516,9 +521,42 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                     for (int q = 0; q < NP; ++q) sum[q] = sum[q] + c3[q];
                 }
             }
+            // MAX_RAYTRACE_DEPTH = 0 with the root shadow rays already traced above: the tree is its root, whose hit is
+            // resolved and whose lights are known -- ads_phong_lighting (glsl:789-840) right here, through the helpers
+            // trace_sample uses (phong_light / phong_accumulate, weight 1), so the frame is the same byte for byte.
+            bool shaded_here = false;
+            if constexpr (!BOUNCE) {
+                shaded_here = have_sb;                                                    // CTA-uniform
+                if (shaded_here) {
+#pragma unroll
+                    for (int q = 0; q < NP; ++q) {
+                        const bool hit = valid[q] && ob3[q] >= 0;
+                        if (COUNT && valid[q]) { cnt.rays++; cnt.nodes++; cnt.hit_nodes += hit; }
+                        if (hit) {
+                            const RtCold* __restrict__ mat = P.cold + ob3[q];
+                            if (COUNT) { cnt.rays += P.n_lights; cnt.shadow_rays += P.n_lights; cnt.pad += P.n_lights - P.n_lit_batch; }
+                            float amb[4], dif[4] = {0, 0, 0, 0}, spc[4] = {0, 0, 0, 0};
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) amb[k] = P.amb_sum[k] * mat->ambient[k];      // glsl:801
+                            const V3 view = normalize3(-dir[q]);                                   // glsl:827
+#pragma unroll
+                            for (int k = 0; k < kShadowBatch; ++k) {
+                                if (k < n_lights_b && !(rsb[q][k] < 1.0f)) {                       // glsl:816
+                                    if (COUNT) cnt.shaded_lights++;
+                                    const RtLightDev* __restrict__ L = P.lights + P.lit[k];
+                                    phong_light(L, mat, mk(L->position[0] - hp[q].x, L->position[1] - hp[q].y, L->position[2] - hp[q].z),
+                                                hn3[q], view, dif, spc);
+                                }
+                            }
+                            sum[q] = sum[q] + phong_accumulate(mk(0.0f, 0.0f, 0.0f), 1.0f, amb, dif, spc, mat);
+                        }
+                    }
+                    if (COUNT) cnt.warp_iters += NP;
+                }
+            }
             // one copy of the bounce machinery in the instruction stream: rolled loop, selected operands
 #pragma unroll 1
-            for (int q = 0; q < (lockstep ? 0 : NP); ++q) {
+            for (int q = 0; q < ((lockstep || shaded_here) ? 0 : NP); ++q) {
                 const V3 dq = q == 0 ? dir[0] : (q == 1 ? dir[1] : dir[2]);
                 const float tq = q == 0 ? best[0] : (q == 1 ? best[1] : best[2]);
                 const int iq = q == 0 ? bidx[0] : (q == 1 ? bidx[1] : bidx[2]);
