@@ -148,7 +148,9 @@ typedef struct rt_options {
                                * also below RT_BLOCK_MIN_OBJECTS objects (test switch); bit 5 = shadow packets without
                                * their fan planes (cone and reach only); bit 6 = bounce rays are not grouped into
                                * packets (per-ray loops); bit 7 = small scenes: shadow rays that start inside a first box
-                               * that holds every lit light (the room) are tested against it all the same */
+                               * that holds every lit light (the room) are tested against it all the same; bit 8 = the
+                               * packet tests go object by object, not through the bounding spheres of groups of 32
+                               * neighbouring objects first (built from 2048 objects up, rt_groups.cu) */
     void* done_flag;          /* optional device pointer to a 32-bit completion word -- typically in ANOTHER GPU's memory,
                                * mapped with rt_ipc_import: done_value is stored there (system-scope release, a one-thread
                                * kernel in stream order behind the render) once every framebuffer store of the call is
@@ -159,6 +161,7 @@ typedef struct rt_options {
 /* Environment variables (read once per process; profiling / tuning aids, results are byte-identical whatever they
  * say):  RT_GROUP_K    bounce rays as grouped packets: (group radius / scene extent)^2, default 0.01
  *        RT_GROUP_COS  ... and the cosine of the largest angle between a group member and its leader, default 0.94
+ *        RT_GROUPS_MIN object count from which the groups of 32 neighbouring objects are built, default 2048
  *        RT_BLOCK_LOG  path: the instrumented twin of the block kernel (rt_options.stats != NULL) dumps one 64-byte
  *                      timing record per block of 48 x 16 pixels there (tools/block_log.py) */
 #define RT_HOST_STORE_AUTO   0

@@ -91,6 +91,20 @@ RTC_FN float packet_radius(float w, bool sph, float grow, float pad1, float pad2
     if (sph) rp = __fmaf_rn(rp, 1.0005f, pad1);
     return __fmaf_rn(rp, 1.000001f, grow);
 }
+// Groups of objects (rt_groups.cu): g = (centre m, R) with R >= |c - m| + packet_radius(member, grow = 0) for every
+// member (c, .).  group_radius is the radius to put into cone_pass / ball_pass in a member's place: whenever one of
+// those tests passes for a member with the same `grow`, it passes for (m, group_radius).  Why: each test compares a
+// function of the centre that changes by at most |c - m| between c and m (the distance to the cone's surface
+// p cos - h sin, -h sin, |v|, |v . nrm|: gradients of length <= 1) with the radius, so R + grow on the right side
+// covers the move.  Two things are not 1-Lipschitz and are covered by the 0.0015 |v| term: the lowering of p^2 by
+// 2e-6 |v|^2 in cone_pass, which may let a member pass whose true distance to the cone is up to 0.0014 |v_member|
+// (<= 0.0014 (|v| + R)) beyond its radius, and the rounding of h, v2 (a few 1e-7 |v|).  R itself carries a relative
+// 1e-4 and an absolute 1e-5 E from the builder.  tests/cone_host.cpp checks the implication on random packets.
+RTC_FN float group_radius(V3 apex, float4 g, float grow) {
+    const V3 v = mk(g.x - apex.x, g.y - apex.y, g.z - apex.z);
+    const float v2 = __fmaf_rn(v.x, v.x, __fmaf_rn(v.y, v.y, __fmul_rn(v.z, v.z)));
+    return __fmaf_rn(sqrt_approx(v2), 0.0015f, __fmaf_rn(g.w, 1.0016f, grow));
+}
 // Rays that start within `radius` of the apex and run toward it stay inside that ball: the bounding sphere
 // (c, rp) can only matter if it reaches into the ball.
 RTC_FN bool ball_pass(V3 apex, float radius, float4 c, float rp) {

@@ -37,6 +37,10 @@
  * block's 8 work items is uneven and its warps wait for each other at the block's barriers (depth 2, round 2: 1k
  * objects 6.7 against 7.6 ms, 2k 9.6 / 9.7, 4k 17.2 / 15.0, 16k 50.8 / 39.3) */
 #define RT_BLOCK_MAX_OBJECTS_BOUNCE 3072
+/* groups of this many neighbouring objects carry a bounding sphere of their own (rt_groups.cu); built from
+ * RT_GROUPS_MIN_OBJECTS hot objects up, for the fast kernel */
+#define RT_GROUP_SIZE 32
+#define RT_GROUPS_MIN_OBJECTS 2048
 #define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
 /* rt_render_block_noalloc: limits of the file-scope scratch array (same values as in include/rt_b200.h, checked in rt_host.cpp) */
 #define RT_NOALLOC_MAX_OBJECTS_DEV 2048
@@ -133,6 +137,10 @@ struct RtParams {
     uint32_t* blk_log;          /* block kernel, instrumented twin only (RT_BLOCK_LOG=path): 16 words per block, see tools/block_log.py */
     int32_t room_skip;          /* 1: hot box 0 holds every lit light (with margin): shadow rays that start inside it too skip it */
     float4 lit_pos[3], lit_dif[3], lit_spc[3];   /* the lit lights (n_lit_batch of them): position, diffuse, specular (glsl:190-196) */
+    const float4* grp;          /* per group: (centre, radius) of a sphere around its members' bounding spheres (rt_groups.cu) */
+    const float4* srec;         /* bounding records in group order: (centre, packet radius before `grow`), 32 per group */
+    const uint32_t* sidx;       /* their hot-list positions */
+    int32_t n_groups;           /* 0: no groups (small scene, strict kernel, or switched off: no_cull bit 8) */
     RtCameraDev cam0;           /* single-frame launches with cams == NULL: the camera uniforms ride in the kernel parameters */
 };
 

@@ -51,6 +51,11 @@ cudaError_t run(const rt_object* d_objs, int n_obj, int32_t* d_box_obj, int32_t*
                 float* d_box_fast, float* d_box_cull, float* d_sph, const RtLightDev* d_lights, int n_lit, const int* lit,
                 float light_reach, float* d_obj_lrec, void* d_scratch, int sm_count, cudaStream_t st);
 }
+namespace rt_groups {
+size_t scratch_bytes(int n_hot, int sm_count);
+cudaError_t run(const float* d_box_cull, const float* d_sph, int n_box, int n_sph, const float* d_extent, float* d_grp, float* d_srec,
+                uint32_t* d_sidx, void* d_scratch, int sm_count, cudaStream_t st);
+}
 namespace rt_strict {
 cudaError_t launch(const RtParams& P, int sm_count, bool count, cudaStream_t stream);
 cudaError_t configure(int device, int* max_smem_optin);
@@ -139,6 +144,10 @@ struct rt_context {
     DevBuf<rt_object> d_objs;                 // device prologue: the raw objects
     DevBuf<uint8_t> d_scratch;                // device prologue: counts, extent, barrier words
     size_t n_objects_dev = 0;
+    DevBuf<float> d_grp, d_srec;              // groups of neighbouring objects (rt_groups.cu): spheres, sorted bounding records
+    DevBuf<uint32_t> d_sidx;                  // hot-list positions of the sorted records
+    DevBuf<uint8_t> d_gscratch;
+    int n_groups = 0;                         // 0: none built for the uploaded scene
     DevBuf<uint32_t> d_blist;                 // block kernel: shadow-candidate lists, one slice per resident CTA
     DevBuf<uint32_t> d_blklog;                // block kernel, RT_BLOCK_LOG=path: per-block timing records of the instrumented twin
     int prologue_mode = RT_PROLOGUE_AUTO;
@@ -327,6 +336,7 @@ int rt_destroy(rt_context* c) {
     c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_obj_lrec.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
     c->d_objs.release(); c->d_scratch.release(); c->d_blist.release(); c->d_blklog.release();
+    c->d_grp.release(); c->d_srec.release(); c->d_sidx.release(); c->d_gscratch.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -354,6 +364,25 @@ int rt_host_alloc(void** ptr, size_t bytes) {
 }
 int rt_host_free(void* ptr) {
     if (ptr) CU(cudaFreeHost(ptr));
+    return RT_OK;
+}
+
+// Groups of 32 neighbouring objects with a bounding sphere each (rt_groups.cu), from the records the prologue left on
+// the device; one launch on the context's stream, behind the prologue, in front of the upload event.
+static int build_groups(rt_context* c) {
+    static const int min_objects = getenv("RT_GROUPS_MIN") ? atoi(getenv("RT_GROUPS_MIN")) : RT_GROUPS_MIN_OBJECTS;
+    const int n_hot = c->n_box + c->n_sph;
+    c->n_groups = 0;
+    if (n_hot < min_objects || n_hot < 1) return RT_OK;
+    const size_t ng = ((size_t)n_hot + RT_GROUP_SIZE - 1) / RT_GROUP_SIZE;
+    CU(c->d_grp.reserve(ng * 4));
+    CU(c->d_srec.reserve(ng * RT_GROUP_SIZE * 4));
+    CU(c->d_sidx.reserve(ng * RT_GROUP_SIZE));
+    CU(c->d_gscratch.reserve(rt_groups::scratch_bytes(n_hot, c->sm_count)));
+    CU(rt_groups::run(c->p_box_cull, c->p_sph, c->n_box, c->n_sph, reinterpret_cast<const float*>(c->p_extent), c->d_grp.p, c->d_srec.p,
+                      c->d_sidx.p, c->d_gscratch.p, c->sm_count, c->stream));
+    g_launches += 1;
+    c->n_groups = (int)ng;
     return RT_OK;
 }
 
@@ -416,6 +445,11 @@ static int upload_host(rt_context* c, const rt_scene* scene) {
     c->max_depth = hs.max_depth;
     c->have_scene = true;
     c->strict_ready = true;
+    {
+        const int rc2 = build_groups(c);
+        if (rc2 != RT_OK) return rc2;
+        if (c->n_groups > 0) CU(cudaEventRecord(c->ev_upload, c->stream));       // the upload now ends with the group kernel
+    }
     // does the first box hold every lit light, 1e-3 (of the half extent) away from its faces?  (all_objects: room_skip)
     c->room_skip = 0;
     if (!hs.box_obj.empty() && hs.n_lit_total > 0) {
@@ -490,6 +524,11 @@ static int upload_device(rt_context* c, const rt_scene* scene) {
     c->have_scene = true;
     c->strict_ready = false;
     c->room_skip = 0;
+    {
+        const int rc2 = build_groups(c);
+        if (rc2 != RT_OK) return rc2;
+        if (c->n_groups > 0) { CU(cudaEventRecord(c->ev_upload, c->stream)); c->upload_recorded = true; }
+    }
     return RT_OK;
 }
 
@@ -612,6 +651,10 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     }
     P.extent = reinterpret_cast<const float*>(c->p_extent);
     P.room_skip = (c->room_skip && !o.strict && !(o.no_cull & 128)) ? 1 : 0;     // bit 7 (test switch): no inside-box shadow skip
+    if (P.packet && c->n_groups > 0 && !(o.no_cull & 256)) {                     // bit 8 (test switch): packet tests object by object
+        P.grp = reinterpret_cast<const float4*>(c->d_grp.p); P.srec = reinterpret_cast<const float4*>(c->d_srec.p);
+        P.sidx = c->d_sidx.p; P.n_groups = c->n_groups;
+    }
     if (P.block) {
         // one list slice per CTA of the persistent grid (at most RT_MAX_CTAS_PER_SM per SM); every hot object fits
         P.blist_stride = c->n_box + c->n_sph;

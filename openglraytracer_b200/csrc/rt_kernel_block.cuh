@@ -22,6 +22,7 @@
 
 constexpr int kBlkW = 2, kBlkH = 4;              // work items per block
 constexpr int kListCap = 2048;                   // primary candidates per block; an overflowing block falls back to packet_trace
+constexpr int kGroupCap = 1024;                  // groups tested per round of block_filter_groups
 constexpr float kBlockMinCos = 0.1f;             // light cones of a block may be wide: they only feed the list, which cannot
                                                  // overflow (list B lives in HBM / L2, one slice of n_hot entries per CTA)
 
@@ -31,7 +32,8 @@ struct BlockShared {
     float mx[kWarps][12];                        // per warp, per light slot: max sin^2, max |L - p|^2, in-cone flag
     float hw[kWarps][4];                         // per warp, per light slot: max distance of a hit point to the block's fan plane
     unsigned count_a, count_b[2];                // count_b: one per sample parity (reset while the other is in use)
-    unsigned pad_;
+    unsigned count_g;                            // groups that met the block's cones (block_filter_groups)
+    uint32_t list_g[kGroupCap];                  // those groups: index | cone mask << 28
     unsigned long long next;
 };
 constexpr int kBlockSharedBytes = (int)((sizeof(BlockShared) + 15) / 16 * 16);
@@ -89,6 +91,78 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
                 if (cm != 0u && pos < (unsigned)cap) list[pos] = (uint32_t)jj[b] | (cm << 28);
             }
         }
+    }
+}
+
+// The same list through the groups of rt_groups.cu: all threads test group spheres (one per thread and trip), then
+// each warp takes a group that met a cone and tests its 32 members, one per lane, against the cones the group met --
+// the member test of block_filter on the same record (its radius comes ready from the builder).  A group that no
+// cone meets has no member that a cone meets (rt_cone.h: group_radius), so the list holds the same objects; their
+// order differs, which candidate_test does not see.  kGroupCap groups per round; barriers in CTA-uniform flow.
+template <bool COUNT, int NC>
+__device__ __forceinline__ void block_filter_groups(const RtParams& P, const WarpCtx& w, BlockShared* bs, const Cone (&cone)[NC], unsigned on,
+                                                    const float (&ball)[NC], float grow, uint32_t* __restrict__ list, int cap,
+                                                    unsigned* __restrict__ counter, RtCounters& cnt) {
+    const unsigned lt_mask = (1u << w.lane) - 1u;
+    const int warp = (int)(threadIdx.x >> 5);
+    for (int g0 = 0; g0 < P.n_groups; g0 += kGroupCap) {
+        if (threadIdx.x == 0) bs->count_g = 0u;
+        __syncthreads();
+        const int g1 = min(P.n_groups, g0 + kGroupCap);
+#pragma unroll 1
+        for (int gb = g0; gb < g1; gb += kThreads) {
+            const int g = gb + (int)threadIdx.x;
+            const bool in = g < g1;
+            const float4 c = __ldg(P.grp + min(g, g1 - 1));
+            unsigned cm = 0u;
+#pragma unroll
+            for (int k = 0; k < NC; ++k) {
+                const bool use_c = NC == 1 || ((on >> k) & 1u), use_b = ball[k] > 0.0f;            // CTA-uniform
+                if (use_c || use_b) {
+                    const float rp = group_radius(cone[k].apex, c, grow);
+                    if (use_c) cm |= cone_pass<NC != 1>(cone[k], c, rp) ? (1u << k) : 0u;
+                    if (use_b) cm |= ball_pass(cone[k].apex, ball[k], c, rp) ? (1u << k) : 0u;
+                }
+            }
+            if (!in) cm = 0u;
+            if (COUNT && in) cnt.packet_tests += (unsigned long long)(NC == 1 ? 1 : __popc(on));
+            const unsigned mask = __ballot_sync(kFull, cm != 0u);
+            if (mask) {
+                unsigned base = 0u;
+                if (w.lane == 0) base = atomicAdd(&bs->count_g, (unsigned)__popc(mask));
+                base = __shfl_sync(kFull, base, 0);
+                if (cm != 0u) bs->list_g[base + (unsigned)__popc(mask & lt_mask)] = (uint32_t)g | (cm << 28);
+            }
+        }
+        __syncthreads();
+        const int ng = (int)bs->count_g;
+#pragma unroll 1
+        for (int e = warp; e < ng; e += kWarps) {
+            const uint32_t ent = bs->list_g[e];
+            const int i = (int)(ent & 0x0fffffffu) * RT_GROUP_SIZE + w.lane;
+            const unsigned gm = ent >> 28;
+            const float4 c = __ldg(P.srec + i);
+            const uint32_t hot = __ldg(P.sidx + i);
+            const float rp = __fmaf_rn(c.w, 1.000001f, grow);      // packet_radius' last step; NaN: no object / never hit
+            unsigned cm = 0u;
+#pragma unroll
+            for (int k = 0; k < NC; ++k) {
+                if ((gm >> k) & 1u) {                              // warp-uniform
+                    if (NC == 1 || ((on >> k) & 1u)) cm |= cone_pass<NC != 1>(cone[k], c, rp) ? (1u << k) : 0u;
+                    if (ball[k] > 0.0f) cm |= ball_pass(cone[k].apex, ball[k], c, rp) ? (1u << k) : 0u;
+                }
+            }
+            if (COUNT) cnt.packet_tests += (unsigned long long)(rp == rp ? __popc(gm) : 0);
+            const unsigned mask = __ballot_sync(kFull, cm != 0u);
+            if (mask) {
+                unsigned base = 0u;
+                if (w.lane == 0) base = atomicAdd(counter, (unsigned)__popc(mask));
+                base = __shfl_sync(kFull, base, 0);
+                const unsigned pos = base + (unsigned)__popc(mask & lt_mask);
+                if (cm != 0u && pos < (unsigned)cap) list[pos] = hot | (cm << 28);
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -233,7 +307,10 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
             cone_close(bc[0], warp_max_nonneg(s2), kFar * 1.001f);
         }
         const float no_ball[1] = {0.0f};
-        if (a_ok) block_filter<SMEM, COUNT, 1>(P, w, bc, 1u, no_ball, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
+        if (a_ok) {                                                             // CTA-uniform, as is P.n_groups
+            if (P.n_groups > 0) block_filter_groups<COUNT, 1>(P, w, bs, bc, 1u, no_ball, 0.0f, bs->list_a, kListCap, &bs->count_a, cnt);
+            else block_filter<SMEM, COUNT, 1>(P, w, bc, 1u, no_ball, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
+        }
         __syncthreads();                                                        // list A complete
         const int na = (int)bs->count_a;
         const bool use_a = a_ok && na <= kListCap;
@@ -440,8 +517,10 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 const bool any_b = on != 0u || ball[0] > 0.0f || ball[1] > 0.0f || ball[2] > 0.0f;
                 // every thread holds the same `on`, balls and cones (all read from shared memory): CTA-uniform.  The list
                 // cannot overflow: one entry per object at most, and the CTA's slice holds n_hot entries.
-                if (any_b)
-                    block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
+                if (any_b) {
+                    if (P.n_groups > 0) block_filter_groups<COUNT, kShadowBatch>(P, w, bs, lc, on, ball, 0.0101f, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
+                    else block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
+                }
                 __syncthreads();                                                    // list B complete
                 const int nb = (int)bs->count_b[s & 1];
                 if (threadIdx.x == 0) bs->count_b[(s + 1) & 1] = 0u;                // its readers (sample s - 1) are past two barriers

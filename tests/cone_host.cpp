@@ -4,6 +4,7 @@
 // cones with fan planes, secondary_packets: groups with scattered origins) and checked against an exact
 // double-precision segment / sphere test.  Prints "<cases> <objects that must pass> <violations>".
 // Built by tests/test_cone_host.py: g++ -O2 -ffp-contract=off.
+#include <algorithm>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -148,7 +149,7 @@ int main(int argc, char** argv) {
     const int cases = argc > 1 ? atoi(argv[1]) : 2000;
     const double E = 19.05;                       // extent of the +-11 room
     const float pad1 = (float)(2e-6 * E), pad2 = (float)(4e-6 * E * E);
-    long must = 0, bad = 0;
+    long must = 0, bad = 0, member_pass = 0, group_bad = 0;
     for (int cs = 0; cs < cases; ++cs) {
         const int n_rays = 4 + (int)(uni() * 93);
         Packet P;
@@ -157,6 +158,8 @@ int main(int argc, char** argv) {
         else if (cs % 3 == 1) shadow_packet(P, n_rays, pad1);
         else group_packet(P, n_rays, pad1);
         // objects: a mix of sizes; half of them placed next to a ray so that near misses and grazing hits are common
+        std::vector<float4> recs;                  // every object's record and un-grown packet radius, for the groups below
+        std::vector<float> rp0s;
         for (int j = 0; j < 400; ++j) {
             const double R = j % 4 == 0 ? uni(0.5, 3.0) : uni(0.02, 0.6);
             D3 c = {uni(-11, 11), uni(-11, 11), uni(-11, 11)};
@@ -168,6 +171,8 @@ int main(int argc, char** argv) {
             // the record the prologue writes: squared radius, padded for boxes (rt_prologue_math.h: padded_radius2)
             const double rp_box = R * 1.0005 + 2e-6 * E;
             const float4 rec = {(float)c.x, (float)c.y, (float)c.z, sph ? (float)(R * R) : (float)(rp_box * rp_box)};
+            recs.push_back(rec);
+            rp0s.push_back(packet_radius(rec.w, sph, 0.0f, pad1, pad2) / 1.000001f * 1.0000002f);   // its value before the last step, rounded up
             const D3 cf = {rec.x, rec.y, rec.z};
             bool hit = false;
             for (int i = 0; i < n_rays && !hit; ++i) hit = seg_dist(P.o[i], P.d[i], 1.0, cf) <= R;
@@ -177,7 +182,48 @@ int main(int argc, char** argv) {
             const bool pass = P.slab ? cone_pass<true>(P.k, rec, rp) : cone_pass<false>(P.k, rec, rp);
             if (!pass) ++bad;
         }
+        // groups (rt_groups.cu): objects of one cell of a 4 x 4 x 4 grid, 8 at a time; the sphere is built as the
+        // kernel builds it (middle of the centres' bounding box, |c - m| and the sum rounded up by 1e-4, + 1e-5 E).
+        // Whatever packet test passes for a member must pass for its group with group_radius.
+        {
+            std::vector<int> order(recs.size());
+            for (size_t j = 0; j < order.size(); ++j) order[j] = (int)j;
+            auto cell = [&](int j) {
+                auto q = [](float v) { int c = (int)((v + 11.0f) * (4.0f / 22.0f)); return c < 0 ? 0 : (c > 3 ? 3 : c); };
+                return (q(recs[j].x) * 4 + q(recs[j].y)) * 4 + q(recs[j].z);
+            };
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cell(a) < cell(b); });
+            const float ball_r = (float)uni(0.05, 4.0);
+            for (size_t g0 = 0; g0 < order.size(); g0 += 8) {
+                const size_t g1 = std::min(order.size(), g0 + 8);
+                float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+                for (size_t e = g0; e < g1; ++e) {
+                    const float4 c = recs[order[e]];
+                    lo[0] = std::fmin(lo[0], c.x); lo[1] = std::fmin(lo[1], c.y); lo[2] = std::fmin(lo[2], c.z);
+                    hi[0] = std::fmax(hi[0], c.x); hi[1] = std::fmax(hi[1], c.y); hi[2] = std::fmax(hi[2], c.z);
+                }
+                const float mx = 0.5f * lo[0] + 0.5f * hi[0], my = 0.5f * lo[1] + 0.5f * hi[1], mz = 0.5f * lo[2] + 0.5f * hi[2];
+                float r = 0.0f;
+                for (size_t e = g0; e < g1; ++e) {
+                    const float4 c = recs[order[e]];
+                    const float dx = c.x - mx, dy = c.y - my, dz = c.z - mz;
+                    r = std::fmax(r, __fmaf_rn(std::sqrt(dx * dx + dy * dy + dz * dz), 1.0001f, rp0s[order[e]]));
+                }
+                const float4 grp = {mx, my, mz, __fmaf_rn(r, 1.0001f, (float)(1e-5 * E))};
+                const float rg = group_radius(P.k.apex, grp, P.grow);
+                const bool g_cone = P.slab ? cone_pass<true>(P.k, grp, rg) : cone_pass<false>(P.k, grp, rg);
+                const bool g_ball = ball_pass(P.k.apex, ball_r, grp, rg);
+                for (size_t e = g0; e < g1; ++e) {
+                    const int j = order[e];
+                    const float rm = packet_radius(recs[j].w, j % 5 == 4, P.grow, pad1, pad2);
+                    const bool m_cone = P.slab ? cone_pass<true>(P.k, recs[j], rm) : cone_pass<false>(P.k, recs[j], rm);
+                    const bool m_ball = ball_pass(P.k.apex, ball_r, recs[j], rm);
+                    member_pass += m_cone + m_ball;
+                    group_bad += (m_cone && !g_cone) + (m_ball && !g_ball);
+                }
+            }
+        }
     }
-    printf("%d %ld %ld\n", cases, must, bad);
+    printf("%d %ld %ld %ld %ld\n", cases, must, bad, member_pass, group_bad);
     return 0;
 }

@@ -19,13 +19,17 @@ def _build(tmp_path, source):
 
 def test_packet_tests_are_conservative(tmp_path):
     exe = _build(tmp_path, os.path.join(ROOT, "tests", "cone_host.cpp"))
-    cases, must, bad = (int(x) for x in subprocess.check_output([str(exe), "3000"]).split())
+    cases, must, bad, member_pass, group_bad = (int(x) for x in subprocess.check_output([str(exe), "3000"]).split())
     assert cases == 3000 and must > 300000        # objects some ray of the packet really hits
     assert bad == 0                               # ... none of them rejected by cone / reach / fan plane
+    # groups of neighbouring objects (rt_groups.cu, rt_cone.h: group_radius): whenever a member passes a cone or
+    # ball test, so does the sphere of its group
+    assert member_pass > 300000 and group_bad == 0
 
 
 def test_the_property_test_has_teeth(tmp_path):
-    """A fan plane 30 % too thin, or bounding radii 20 % too small, must show up as violations."""
+    """A fan plane 30 % too thin, or bounding radii 20 % too small, must show up as violations; so must group
+    spheres 10 % too small."""
     src = open(os.path.join(ROOT, "tests", "cone_host.cpp")).read()
     for old, new in (("cone_fan(P.k, nrm, hmax, pad1);", "cone_fan(P.k, nrm, hmax * 0.7f, pad1);"),
                      ("const float rp = packet_radius(", "const float rp = 0.8f * packet_radius(")):
@@ -33,5 +37,12 @@ def test_the_property_test_has_teeth(tmp_path):
         mutant = tmp_path / "mutant.cpp"
         mutant.write_text(src.replace(old, new))
         exe = _build(tmp_path, mutant)
-        _, _, bad = (int(x) for x in subprocess.check_output([str(exe), "600"]).split())
+        _, _, bad, _, _ = (int(x) for x in subprocess.check_output([str(exe), "600"]).split())
         assert bad > 0
+    old = "const float rg = group_radius(P.k.apex, grp, P.grow);"
+    assert src.count(old) == 1
+    mutant = tmp_path / "mutant.cpp"
+    mutant.write_text(src.replace(old, "const float rg = 0.9f * group_radius(P.k.apex, grp, P.grow);"))
+    exe = _build(tmp_path, mutant)
+    _, _, _, _, group_bad = (int(x) for x in subprocess.check_output([str(exe), "600"]).split())
+    assert group_bad > 0

@@ -266,7 +266,8 @@ def test_device_prologue_matches_host_prologue_and_oracle():
                               (rt.scaled_scene(4096, max_depth=0), rt.builtin_camera(0.0), 256, 144)]:
             before = rt.kernel_launch_count()
             a = dev.render(sc, cam, w, h)
-            assert rt.kernel_launch_count() == before + 2          # the fused prologue kernel + the render kernel
+            # the fused prologue kernel + the render kernel (+ the group kernel of rt_groups.cu from 2048 objects up)
+            assert rt.kernel_launch_count() == before + 2 + (1 if len(sc.objects) >= 2048 else 0)
             b = host.render(sc, cam, w, h)
             same = (a == b).all(axis=2).mean()
             assert same >= 0.999, same
@@ -633,3 +634,29 @@ def test_inside_box_shadow_skip_changes_nothing(tracer):
     off, st_off = tracer.render(sc, rt.builtin_camera(0.0), 320, 180, want_stats=True, no_cull=128)
     assert np.array_equal(on, off) and st_on["box_tests"] == st_off["box_tests"]
     _check(on, ob.render(sc, rt.builtin_camera(0.0), 320, 180), "room last")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,w,h,depth", [(2500, 480, 270, 1), (4096, 640, 360, 0), (65536, 1920, 1080, 0)])
+def test_object_groups_change_nothing(tracer, n, w, h, depth):
+    """From RT_GROUPS_MIN_OBJECTS objects up the packet tests first ask a bounding sphere around each group of 32
+    neighbouring objects (rt_groups.cu).  A group may only be skipped when none of its members could pass:
+    frames are BYTE-identical with the groups off (no_cull bit 8) and with every slab test run (bit 0); the same
+    rays are cast, fewer packet tests are executed."""
+    sc, cam = rt.scaled_scene(n, max_depth=depth), rt.builtin_camera(0.0)
+    on, st_on = tracer.render(sc, cam, w, h, want_stats=True)
+    off, st_off = tracer.render(sc, cam, w, h, want_stats=True, no_cull=256)
+    assert np.array_equal(on, off)
+    assert np.array_equal(on, tracer.render(sc, cam, w, h))
+    assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=256))
+    if n <= 4096:
+        assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=1))
+    assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
+    assert st_on["shaded_lights"] == st_off["shaded_lights"]
+    assert 0 < st_on["packet_tests"] < st_off["packet_tests"]
+    # bands through the grouped filter
+    canvas = np.empty_like(on)
+    edges = [0, 37, 90, h]
+    for y0, y1 in zip(edges[:-1], edges[1:]):
+        canvas[y0:y1] = tracer.render(sc, cam, w, h, y0=y0, y1=y1, band_only=True, no_cull=16)
+    assert np.array_equal(canvas, on)
