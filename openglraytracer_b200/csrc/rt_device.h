@@ -41,6 +41,7 @@
  * RT_GROUPS_MIN_OBJECTS hot objects up, for the fast kernel */
 #define RT_GROUP_SIZE 32
 #define RT_GROUPS_MIN_OBJECTS 2048
+#define RT_GROUPS_MIN_OBJECTS_BOUNCE 4096      /* ... and used at depth > 0 only from this many */
 #define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
 /* rt_render_block_noalloc: limits of the file-scope scratch array (same values as in include/rt_b200.h, checked in rt_host.cpp) */
 #define RT_NOALLOC_MAX_OBJECTS_DEV 2048
@@ -138,7 +139,7 @@ struct RtParams {
     int32_t room_skip;          /* 1: hot box 0 holds every lit light (with margin): shadow rays that start inside it too skip it */
     float4 lit_pos[3], lit_dif[3], lit_spc[3];   /* the lit lights (n_lit_batch of them): position, diffuse, specular (glsl:190-196) */
     const float4* grp;          /* per group: (centre, radius) of a sphere around its members' bounding spheres (rt_groups.cu) */
-    const float4* srec;         /* bounding records in group order: (centre, packet radius before `grow`), 32 per group */
+    const float4* srec;         /* the bounding records (box_cull / sph_hot entries) in group order, 32 per group; w = NaN: none */
     const uint32_t* sidx;       /* their hot-list positions */
     int32_t n_groups;           /* 0: no groups (small scene, strict kernel, or switched off: no_cull bit 8) */
     RtCameraDev cam0;           /* single-frame launches with cams == NULL: the camera uniforms ride in the kernel parameters */

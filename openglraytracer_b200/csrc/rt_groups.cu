@@ -15,8 +15,8 @@
  *   0  bounding box of the centres
  *   1  24-bit Morton keys (8 bits per axis), stable LSD radix sort of (key, hot index) in three 8-bit passes --
  *      equal keys keep the hot-list order, so the result does not depend on scheduling
- *   2  one warp per group: the sorted bounding records (centre, un-grown packet radius -- the sqrt of
- *      rt_cone.h: packet_radius paid once per upload), their hot-list positions, the group sphere
+ *   2  one warp per group: the bounding records in sorted order (a copy: a group's 32 records are one 512-byte
+ *      read), their hot-list positions, the group sphere
  */
 #include <cuda_runtime.h>
 #include <math_constants.h>
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(kThreads) groups_kernel(Arrays A, int chunk) {
         float r = valid ? __fmaf_rn(sqrtf(dx * dx + dy * dy + dz * dz), 1.0001f, rp0) : -CUDART_INF_F;
         for (int off = 16; off > 0; off >>= 1) r = fmaxf(r, __shfl_xor_sync(kFull, r, off));
         if (lane == 0) A.grp[g] = any ? make_float4(mx, my, mz, __fmaf_rn(r, 1.0001f, 1e-5f * E)) : make_float4(0.0f, 0.0f, 0.0f, CUDART_NAN_F);
-        A.srec[i] = make_float4(c.x, c.y, c.z, valid ? rp0 : CUDART_NAN_F);
+        A.srec[i] = make_float4(c.x, c.y, c.z, valid ? c.w : CUDART_NAN_F);       // NaN: passes no packet test
         A.sidx[i] = (uint32_t)hot;
     }
 }

@@ -96,12 +96,12 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
 
 // The same list through the groups of rt_groups.cu: all threads test group spheres (one per thread and trip), then
 // each warp takes a group that met a cone and tests its 32 members, one per lane, against the cones the group met --
-// the member test of block_filter on the same record (its radius comes ready from the builder).  A group that no
+// the member test of block_filter on a copy of the same record.  A group that no
 // cone meets has no member that a cone meets (rt_cone.h: group_radius), so the list holds the same objects; their
 // order differs, which candidate_test does not see.  kGroupCap groups per round; barriers in CTA-uniform flow.
 template <bool COUNT, int NC>
 __device__ __forceinline__ void block_filter_groups(const RtParams& P, const WarpCtx& w, BlockShared* bs, const Cone (&cone)[NC], unsigned on,
-                                                    const float (&ball)[NC], float grow, uint32_t* __restrict__ list, int cap,
+                                                    const float (&ball)[NC], float grow, float pad1, float pad2, uint32_t* __restrict__ list, int cap,
                                                     unsigned* __restrict__ counter, RtCounters& cnt) {
     const unsigned lt_mask = (1u << w.lane) - 1u;
     const int warp = (int)(threadIdx.x >> 5);
@@ -143,7 +143,7 @@ __device__ __forceinline__ void block_filter_groups(const RtParams& P, const War
             const unsigned gm = ent >> 28;
             const float4 c = __ldg(P.srec + i);
             const uint32_t hot = __ldg(P.sidx + i);
-            const float rp = __fmaf_rn(c.w, 1.000001f, grow);      // packet_radius' last step; NaN: no object / never hit
+            const float rp = packet_radius(c.w, hot >= (uint32_t)P.n_box, grow, pad1, pad2);      // NaN: no object / never hit
             unsigned cm = 0u;
 #pragma unroll
             for (int k = 0; k < NC; ++k) {
@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
         }
         const float no_ball[1] = {0.0f};
         if (a_ok) {                                                             // CTA-uniform, as is P.n_groups
-            if (P.n_groups > 0) block_filter_groups<COUNT, 1>(P, w, bs, bc, 1u, no_ball, 0.0f, bs->list_a, kListCap, &bs->count_a, cnt);
+            if (P.n_groups > 0) block_filter_groups<COUNT, 1>(P, w, bs, bc, 1u, no_ball, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
             else block_filter<SMEM, COUNT, 1>(P, w, bc, 1u, no_ball, 0.0f, pk_pad1, pk_pad2, bs->list_a, kListCap, &bs->count_a, cnt);
         }
         __syncthreads();                                                        // list A complete
@@ -518,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 // every thread holds the same `on`, balls and cones (all read from shared memory): CTA-uniform.  The list
                 // cannot overflow: one entry per object at most, and the CTA's slice holds n_hot entries.
                 if (any_b) {
-                    if (P.n_groups > 0) block_filter_groups<COUNT, kShadowBatch>(P, w, bs, lc, on, ball, 0.0101f, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
+                    if (P.n_groups > 0) block_filter_groups<COUNT, kShadowBatch>(P, w, bs, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
                     else block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
                 }
                 __syncthreads();                                                    // list B complete

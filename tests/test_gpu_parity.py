@@ -637,7 +637,7 @@ def test_inside_box_shadow_skip_changes_nothing(tracer):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n,w,h,depth", [(2500, 480, 270, 1), (4096, 640, 360, 0), (65536, 1920, 1080, 0)])
+@pytest.mark.parametrize("n,w,h,depth", [(2500, 480, 270, 0), (5000, 480, 270, 2), (4096, 640, 360, 0), (65536, 1920, 1080, 0)])
 def test_object_groups_change_nothing(tracer, n, w, h, depth):
     """From RT_GROUPS_MIN_OBJECTS objects up the packet tests first ask a bounding sphere around each group of 32
     neighbouring objects (rt_groups.cu).  A group may only be skipped when none of its members could pass:
@@ -649,8 +649,11 @@ def test_object_groups_change_nothing(tracer, n, w, h, depth):
     assert np.array_equal(on, off)
     assert np.array_equal(on, tracer.render(sc, cam, w, h))
     assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=256))
-    if n <= 4096:
+    if n <= 5000:
         assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=1))
+        # the per-warp kernel and the block kernel, each with and without the groups
+        for mode in (8, 8 | 256, 16, 16 | 256):
+            assert np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=mode)), mode
     assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
     assert st_on["shaded_lights"] == st_off["shaded_lights"]
     assert 0 < st_on["packet_tests"] < st_off["packet_tests"]
