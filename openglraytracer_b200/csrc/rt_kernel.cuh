@@ -912,16 +912,100 @@ __device__ __forceinline__ void candidate_test(const RtParams& P, RaySet& rs, in
     }
 }
 
+// packet_trace through the groups of rt_groups.cu (its own function: the object-by-object loop below keeps its
+// registers and its place in the instruction cache).
+template <bool COUNT, int NC>
+__device__ __noinline__ void packet_trace_groups(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
+                                                 float grow, float live_min, float pad1, float pad2, bool shared, const V3* __restrict__ o_in,
+                                                 const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
+                                                 RtCounters& cnt, unsigned want) {
+    constexpr int R = kShadowBatch;
+    RaySet rs;
+    rayset_load(rs, o_in, d_in, best_io, bidx_io);
+    Cone cone[NC];
+#pragma unroll
+    for (int k = 0; k < NC; ++k) cone[k] = cone_in[k];
+    const int lane = w.lane;
+    // Groups of 32 neighbouring objects (rt_groups.cu): one group sphere per lane and trip; the members of a
+    // group that met a cone are one 512-byte read, one member per lane, tested as the loops below test them.
+    // A group no cone meets has no member a cone meets (rt_cone.h: group_radius), so the same candidates
+    // reach candidate_test; their order differs, which its accept rule does not see.
+    const int ng = P.n_groups;
+    float4 g_next = __ldg(P.grp + min(lane, ng - 1));
+    for (int g0 = 0; g0 < ng; g0 += 32) {
+        if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
+        const float4 gc = g_next;
+        g_next = __ldg(P.grp + min(g0 + 32 + lane, ng - 1));
+        unsigned cm = 0u;
+#pragma unroll
+        for (int k = 0; k < NC; ++k)
+            if (NC == 1 || ((on >> k) & 1u)) cm |= cone_pass(cone[k], gc, group_radius(cone[k].apex, gc, grow)) ? (1u << k) : 0u;
+        if (g0 + lane >= ng) cm = 0u;
+        if (COUNT && g0 + lane < ng) cnt.packet_tests += (unsigned long long)(NC == 1 ? 1 : __popc(on));
+        unsigned gmask = __ballot_sync(kFull, cm != 0u);
+        if (gmask == 0u) continue;
+        int gs = __ffs(gmask) - 1;
+        gmask &= gmask - 1u;
+        float4 c_n = __ldg(P.srec + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
+        uint32_t h_n = __ldg(P.sidx + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
+        unsigned cm_n = __shfl_sync(kFull, cm, gs);
+        for (;;) {
+            const float4 c = c_n;
+            const int hot = (int)h_n;
+            const unsigned cmg = cm_n;
+            const bool more = gmask != 0u;                   // warp-uniform: the next group's records in flight
+            if (more) {
+                gs = __ffs(gmask) - 1;
+                gmask &= gmask - 1u;
+                c_n = __ldg(P.srec + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
+                h_n = __ldg(P.sidx + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
+                cm_n = __shfl_sync(kFull, cm, gs);
+            }
+            const float rp = packet_radius(c.w, hot >= P.n_box, grow, pad1, pad2);       // NaN: no object there
+            bool pass = false;
+#pragma unroll
+            for (int k = 0; k < NC; ++k)
+                if ((cmg >> k) & 1u) pass = pass | cone_pass(cone[k], c, rp);              // warp-uniform
+            if (COUNT) cnt.packet_tests += (unsigned long long)(rp == rp ? __popc(cmg) : 0);
+            unsigned mask = __ballot_sync(kFull, pass);
+            while (mask) {
+                const int src = __ffs(mask) - 1;
+                mask &= mask - 1u;
+                const int hot_s = __shfl_sync(kFull, hot, src);
+                const float4 cc = make_float4(__shfl_sync(kFull, c.x, src), __shfl_sync(kFull, c.y, src),
+                                              __shfl_sync(kFull, c.z, src), __shfl_sync(kFull, c.w, src));
+                candidate_test<COUNT>(P, rs, hot_s, cc, shared, live_min, want, cnt);
+            }
+            if (!more) break;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) { best_io[r] = rs.best[r]; bidx_io[r] = rs.bidx[r]; }
+}
+
+template <bool SMEM, bool COUNT, int NC>
+__device__ __noinline__ void packet_trace_objects(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
+                                                  float grow, float live_min, float pad1, float pad2, bool shared, const V3* __restrict__ o_in,
+                                                  const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
+                                                  RtCounters& cnt, unsigned want);
+template <bool SMEM, bool COUNT, int NC>
+__device__ __forceinline__ void packet_trace(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
+                                             float grow, float live_min, float pad1, float pad2, bool shared, const V3* __restrict__ o_in,
+                                             const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
+                                             RtCounters& cnt, unsigned want = 7u) {
+    if (P.n_groups > 0) packet_trace_groups<COUNT, NC>(P, w, cone_in, on, grow, live_min, pad1, pad2, shared, o_in, d_in, best_io, bidx_io, cnt, want);      // kernel-uniform
+    else packet_trace_objects<SMEM, COUNT, NC>(P, w, cone_in, on, grow, live_min, pad1, pad2, shared, o_in, d_in, best_io, bidx_io, cnt, want);
+}
 // The whole object loop for one packet of 3 rays per lane: the primary rays of a work item (closest
 // hit: live_min = smallest positive float, glsl:753-776) or shadow rays of the warp's hit points (any hit
 // below t = 1: live_min = 1, glsl:816).  One copy in the instruction stream for both (out of line,
 // runtime switches): with 16 warps per SM in different phases of a frame the large-scene kernels are
 // instruction-cache bound, not issue bound.
 template <bool SMEM, bool COUNT, int NC>
-__device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
+__device__ __noinline__ void packet_trace_objects(const RtParams& P, WarpCtx& w, const Cone* __restrict__ cone_in, unsigned on,
                                           float grow, float live_min, float pad1, float pad2, bool shared, const V3* __restrict__ o_in,
                                           const V3* __restrict__ d_in, float* __restrict__ best_io, int* __restrict__ bidx_io,
-                                          RtCounters& cnt, unsigned want = 7u) {
+                                          RtCounters& cnt, unsigned want) {
     constexpr int R = kShadowBatch;
     RaySet rs;
     rayset_load(rs, o_in, d_in, best_io, bidx_io);
@@ -939,64 +1023,6 @@ __device__ __noinline__ void packet_trace(const RtParams& P, WarpCtx& w, const C
     // flight (a warp's pass over the scene is latency bound otherwise: one 3 KB tile ahead was not enough).
     constexpr int kSlots = (2 * kTileBytes) / (W * 16);
     constexpr int kAhead = kSlots - 1;
-    if (P.n_groups > 0) {                                        // kernel-uniform
-        // Groups of 32 neighbouring objects (rt_groups.cu): one group sphere per lane and trip; the members of a
-        // group that met a cone are one 512-byte read, one member per lane, tested as the loops below test them.
-        // A group no cone meets has no member a cone meets (rt_cone.h: group_radius), so the same candidates
-        // reach candidate_test; their order differs, which its accept rule does not see.
-        const int ng = P.n_groups;
-        float4 g_next = __ldg(P.grp + min(lane, ng - 1));
-        for (int g0 = 0; g0 < ng; g0 += 32) {
-            if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
-            const float4 gc = g_next;
-            g_next = __ldg(P.grp + min(g0 + 32 + lane, ng - 1));
-            unsigned cm = 0u;
-#pragma unroll
-            for (int k = 0; k < NC; ++k)
-                if (NC == 1 || ((on >> k) & 1u)) cm |= cone_pass(cone[k], gc, group_radius(cone[k].apex, gc, grow)) ? (1u << k) : 0u;
-            if (g0 + lane >= ng) cm = 0u;
-            if (COUNT && g0 + lane < ng) cnt.packet_tests += (unsigned long long)(NC == 1 ? 1 : __popc(on));
-            unsigned gmask = __ballot_sync(kFull, cm != 0u);
-            if (gmask == 0u) continue;
-            int gs = __ffs(gmask) - 1;
-            gmask &= gmask - 1u;
-            float4 c_n = __ldg(P.srec + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
-            uint32_t h_n = __ldg(P.sidx + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
-            unsigned cm_n = __shfl_sync(kFull, cm, gs);
-            for (;;) {
-                const float4 c = c_n;
-                const int hot = (int)h_n;
-                const unsigned cmg = cm_n;
-                const bool more = gmask != 0u;                   // warp-uniform: the next group's records in flight
-                if (more) {
-                    gs = __ffs(gmask) - 1;
-                    gmask &= gmask - 1u;
-                    c_n = __ldg(P.srec + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
-                    h_n = __ldg(P.sidx + (size_t)(g0 + gs) * RT_GROUP_SIZE + lane);
-                    cm_n = __shfl_sync(kFull, cm, gs);
-                }
-                const float rp = packet_radius(c.w, hot >= P.n_box, grow, pad1, pad2);       // NaN: no object there
-                bool pass = false;
-#pragma unroll
-                for (int k = 0; k < NC; ++k)
-                    if ((cmg >> k) & 1u) pass = pass | cone_pass(cone[k], c, rp);              // warp-uniform
-                if (COUNT) cnt.packet_tests += (unsigned long long)(rp == rp ? __popc(cmg) : 0);
-                unsigned mask = __ballot_sync(kFull, pass);
-                while (mask) {
-                    const int src = __ffs(mask) - 1;
-                    mask &= mask - 1u;
-                    const int hot_s = __shfl_sync(kFull, hot, src);
-                    const float4 cc = make_float4(__shfl_sync(kFull, c.x, src), __shfl_sync(kFull, c.y, src),
-                                                  __shfl_sync(kFull, c.z, src), __shfl_sync(kFull, c.w, src));
-                    candidate_test<COUNT>(P, rs, hot_s, cc, shared, live_min, want, cnt);
-                }
-                if (!more) break;
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) { best_io[r] = rs.best[r]; bidx_io[r] = rs.bidx[r]; }
-        return;
-    }
     for (int part = 0; part < 2; ++part) {
         // no live ray left in the warp (shadow rays: every one occluded, glsl:816 needs ANY occluder)
         if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
