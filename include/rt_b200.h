@@ -150,7 +150,9 @@ typedef struct rt_options {
                                * packets (per-ray loops); bit 7 = small scenes: shadow rays that start inside a first box
                                * that holds every lit light (the room) are tested against it all the same; bit 8 = the
                                * packet tests go object by object, not through the bounding spheres of groups of 32
-                               * neighbouring objects first (built from 2048 objects up, rt_groups.cu) */
+                               * neighbouring objects first (built from 2048 objects up, rt_groups.cu); bit 9 = block
+                               * kernel: one shadow cone per warp and light, also for a warp whose hit points lie at
+                               * several depths (otherwise up to three cones, one per cluster of hit points) */
     void* done_flag;          /* optional device pointer to a 32-bit completion word -- typically in ANOTHER GPU's memory,
                                * mapped with rt_ipc_import: done_value is stored there (system-scope release, a one-thread
                                * kernel in stream order behind the render) once every framebuffer store of the call is

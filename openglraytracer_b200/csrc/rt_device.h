@@ -42,6 +42,7 @@
 #define RT_GROUP_SIZE 32
 #define RT_GROUPS_MIN_OBJECTS 2048
 #define RT_GROUPS_MIN_OBJECTS_BOUNCE 4096      /* ... and used at depth > 0 only from this many */
+#define RT_BLOCK_REC_CAP 8192      /* bounding records kept next to a CTA's shadow-candidate list (16 bytes each) */
 #define RT_MAX_CTAS_PER_SM 4      /* upper bound of the persistent grid per SM (list slices of the block kernel) */
 /* rt_render_block_noalloc: limits of the file-scope scratch array (same values as in include/rt_b200.h, checked in rt_host.cpp) */
 #define RT_NOALLOC_MAX_OBJECTS_DEV 2048
@@ -131,6 +132,8 @@ struct RtParams {
     int32_t block;              /* 1: CTA-level packet tests (blocks of 2 x 4 work items share the pass over the scene) */
     uint32_t* blist;            /* block kernel: per-CTA shadow-candidate lists, blist_stride entries each */
     int32_t blist_stride;
+    float4* brec;               /* ... and, per CTA, the bounding records of the first brec_cap entries of its list (0: none) */
+    int32_t brec_cap;
     const float* extent;        /* scene extent E (max |centre| + radius over objects and lights), written by the prologue */
     int32_t fan;                /* 1: shadow packets of the block kernel also carry a fan plane (rt_kernel.cuh: Cone::nrm) */
     float group_cos;            /* bounce rays join a group when their direction is within this cosine of the leader's */
@@ -142,6 +145,7 @@ struct RtParams {
     const float4* srec;         /* the bounding records (box_cull / sph_hot entries) in group order, 32 per group; w = NaN: none */
     const uint32_t* sidx;       /* their hot-list positions */
     int32_t n_groups;           /* 0: no groups (small scene, strict kernel, or switched off: no_cull bit 8) */
+    int32_t split_cones;        /* 1: block kernel: a warp whose hit points spread wide as seen from a light gives them a cone per cluster */
     RtCameraDev cam0;           /* single-frame launches with cams == NULL: the camera uniforms ride in the kernel parameters */
 };
 

@@ -148,6 +148,7 @@ struct rt_context {
     DevBuf<uint32_t> d_sidx;                  // hot-list positions of the sorted records
     DevBuf<uint8_t> d_gscratch;
     int n_groups = 0;                         // 0: none built for the uploaded scene
+    DevBuf<float> d_brec;                     // ... and the bounding records of each list's first RT_BLOCK_REC_CAP entries
     DevBuf<uint32_t> d_blist;                 // block kernel: shadow-candidate lists, one slice per resident CTA
     DevBuf<uint32_t> d_blklog;                // block kernel, RT_BLOCK_LOG=path: per-block timing records of the instrumented twin
     int prologue_mode = RT_PROLOGUE_AUTO;
@@ -335,7 +336,7 @@ int rt_destroy(rt_context* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->d_box_fast.release(); c->d_box_strict.release(); c->d_box_cull.release(); c->d_obj_lrec.release(); c->d_sph.release();
     c->d_box_obj.release(); c->d_sph_obj.release(); c->d_cold.release();
-    c->d_objs.release(); c->d_scratch.release(); c->d_blist.release(); c->d_blklog.release();
+    c->d_objs.release(); c->d_scratch.release(); c->d_blist.release(); c->d_brec.release(); c->d_blklog.release();
     c->d_grp.release(); c->d_srec.release(); c->d_sidx.release(); c->d_gscratch.release();
     c->d_lights.release(); c->d_cams.release(); c->d_out.release(); c->d_cnt.release(); c->d_tile.release();
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -651,6 +652,7 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
     }
     P.extent = reinterpret_cast<const float*>(c->p_extent);
     P.room_skip = (c->room_skip && !o.strict && !(o.no_cull & 128)) ? 1 : 0;     // bit 7 (test switch): no inside-box shadow skip
+    P.split_cones = (o.no_cull & 512) ? 0 : 1;                                   // bit 9 (test switch): one shadow cone per warp and light
     // groups of neighbouring objects: with bounce rays they pay from about 4k objects (depth 2, 1080p: 2k objects 10.3
     // against 9.9 ms without, 4k 15.6 / 15.9, 16k 30.6 / 39.1; depth 0: 4k 0.47 / 0.51, 16k 0.77 / 0.93, 64k 1.15 / 2.01)
     const bool groups_pay = c->max_depth == 0 || c->n_box + c->n_sph >= RT_GROUPS_MIN_OBJECTS_BOUNCE;
@@ -663,6 +665,9 @@ int rt_render_uploaded(rt_context* c, const rt_camera* cameras, int n_frames,
         P.blist_stride = c->n_box + c->n_sph;
         CU(c->d_blist.reserve((size_t)RT_MAX_CTAS_PER_SM * c->sm_count * (size_t)P.blist_stride));
         P.blist = c->d_blist.p;
+        P.brec_cap = P.blist_stride < RT_BLOCK_REC_CAP ? P.blist_stride : RT_BLOCK_REC_CAP;
+        CU(c->d_brec.reserve((size_t)RT_MAX_CTAS_PER_SM * c->sm_count * (size_t)P.brec_cap * 4));
+        P.brec = reinterpret_cast<float4*>(c->d_brec.p);
     }
     P.n_lit = (P.cull && !P.packet && !(o.no_cull & 2)) ? c->n_lit : 0;
     P.n_lit_batch = c->n_lit_total <= 3 ? c->n_lit_total : -1;
@@ -841,6 +846,7 @@ int rt_render_block_noalloc(rt_context* c, const rt_camera* cameras, int n_frame
     P.tiles_x = (width + 7) / 8; P.tiles_y = (band_rows + 3) / 4;
     P.cull = 1; P.packet = 1; P.block = 1;              // this entry point IS the block kernel
     P.fan = (o.no_cull & 32) ? 0 : 1;
+    P.split_cones = (o.no_cull & 512) ? 0 : 1;
     {
         static const float group_k = getenv("RT_GROUP_K") ? (float)atof(getenv("RT_GROUP_K")) : 0.01f;
         static const float group_cos = getenv("RT_GROUP_COS") ? (float)atof(getenv("RT_GROUP_COS")) : 0.94f;

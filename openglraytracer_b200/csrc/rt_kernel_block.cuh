@@ -23,6 +23,10 @@
 constexpr int kBlkW = 2, kBlkH = 4;              // work items per block
 constexpr int kListCap = 2048;                   // primary candidates per block; an overflowing block falls back to packet_trace
 constexpr int kGroupCap = 1024;                  // groups tested per round of block_filter_groups
+constexpr int kSplitMinList = 128;               // root shadow rays of a warp: from this many candidates in the block's list ...
+constexpr float kSplitSin2 = 0.0025f;            // ... and a cone wider than sin 0.05 (2.9 degrees) the warp's hit points go in clusters
+constexpr float kSplitCos = 0.995f;              // a cluster: directions from the light within 5.7 degrees of its leader's
+constexpr int kClusters = 3;                     // the last one takes what the others left
 constexpr float kBlockMinCos = 0.1f;             // light cones of a block may be wide: they only feed the list, which cannot
                                                  // overflow (list B lives in HBM / L2, one slice of n_hot entries per CTA)
 
@@ -53,7 +57,7 @@ __device__ __forceinline__ unsigned smid() {
 template <bool SMEM, bool COUNT, int NC>
 __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w, const Cone (&cone)[NC], unsigned on,
                                              const float (&ball)[NC], float grow, float pad1, float pad2, uint32_t* __restrict__ list, int cap,
-                                             unsigned* __restrict__ counter, RtCounters& cnt) {
+                                             unsigned* __restrict__ counter, RtCounters& cnt, float4* __restrict__ rec_list = nullptr, int rec_cap = 0) {
     const int n_hot = P.n_box + P.n_sph;
     const unsigned lt_mask = (1u << w.lane) - 1u;
     constexpr int B = 4;                          // records in flight per thread (L2 latency when streaming)
@@ -89,6 +93,7 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
                 base = __shfl_sync(kFull, base, 0);
                 const unsigned pos = base + (unsigned)__popc(mask & lt_mask);
                 if (cm != 0u && pos < (unsigned)cap) list[pos] = (uint32_t)jj[b] | (cm << 28);
+                if (cm != 0u && pos < (unsigned)rec_cap) rec_list[pos] = c[b];
             }
         }
     }
@@ -102,7 +107,7 @@ __device__ __forceinline__ void block_filter(const RtParams& P, const WarpCtx& w
 template <bool COUNT, int NC>
 __device__ __forceinline__ void block_filter_groups(const RtParams& P, const WarpCtx& w, BlockShared* bs, const Cone (&cone)[NC], unsigned on,
                                                     const float (&ball)[NC], float grow, float pad1, float pad2, uint32_t* __restrict__ list, int cap,
-                                                    unsigned* __restrict__ counter, RtCounters& cnt) {
+                                                    unsigned* __restrict__ counter, RtCounters& cnt, float4* __restrict__ rec_list = nullptr, int rec_cap = 0) {
     const unsigned lt_mask = (1u << w.lane) - 1u;
     const int warp = (int)(threadIdx.x >> 5);
     for (int g0 = 0; g0 < P.n_groups; g0 += kGroupCap) {
@@ -160,6 +165,7 @@ __device__ __forceinline__ void block_filter_groups(const RtParams& P, const War
                 base = __shfl_sync(kFull, base, 0);
                 const unsigned pos = base + (unsigned)__popc(mask & lt_mask);
                 if (cm != 0u && pos < (unsigned)cap) list[pos] = hot | (cm << 28);
+                if (cm != 0u && pos < (unsigned)rec_cap) rec_list[pos] = c;
             }
         }
         __syncthreads();
@@ -172,30 +178,49 @@ template <bool SMEM, bool COUNT, bool GLOB>
 __device__ __noinline__ void list_trace(const RtParams& P, const WarpCtx& w, const uint32_t* __restrict__ list, int count, unsigned kbit,
                                         const Cone* __restrict__ cone_in, int mode, float ball_r, float grow, float live_min, float pad1, float pad2,
                                         bool shared, const V3* __restrict__ o_in, const V3* __restrict__ d_in,
-                                        float* __restrict__ best_io, int* __restrict__ bidx_io, RtCounters& cnt) {
+                                        float* __restrict__ best_io, int* __restrict__ bidx_io, RtCounters& cnt,
+                                        const float4* __restrict__ rec_list = nullptr, int rec_cap = 0,
+                                        const float* __restrict__ more_cones = nullptr, int n_more = 0) {
     RaySet rs;
     rayset_load(rs, o_in, d_in, best_io, bidx_io);
     const Cone cone = cone_in[0];
     const int lane = w.lane;
     // GLOB: the list was written to global memory by this CTA during this launch: coherent (L2) loads, the next 32
-    // entries in flight while the current ones are tested
+    // entries in flight while the current ones are tested.  rec_list: the filter left the first rec_cap entries'
+    // bounding records next to the list (one contiguous read per trip; fetching them by hot-list position is 32
+    // scattered L2 reads per trip, which is what a warp's walk over a list of thousands of entries waits for).
+    const int n_rec = GLOB ? min(count, rec_cap) : 0;
     uint32_t ent_next = lane < count ? (GLOB ? __ldcg(list + lane) : list[lane]) : 0u;
+    float4 rec_next = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (GLOB && lane < n_rec) rec_next = __ldcg(rec_list + lane);
     for (int e0 = 0; e0 < count; e0 += 32) {
         if (!__any_sync(kFull, rs.best[0] >= live_min || rs.best[1] >= live_min || rs.best[2] >= live_min)) break;
         const int e = e0 + lane;
         const uint32_t ent = ent_next;
+        const float4 rec = rec_next;
         ent_next = e + 32 < count ? (GLOB ? __ldcg(list + e + 32) : list[e + 32]) : 0u;
+        if (GLOB && e + 32 < n_rec) rec_next = __ldcg(rec_list + e + 32);
         const int hot = (int)(ent & 0x0fffffffu);
         const bool sel = e < count && ((ent >> 28) & kbit) != 0u;
         const bool sph = hot >= P.n_box;
         float4 c;
         if (SMEM) c = smem_f4[sph ? w.sph_off4 + (uint32_t)(hot - P.n_box) : w.box_off4 + (uint32_t)hot];
+        else if (GLOB && e < n_rec) c = rec;
         else c = sph ? __ldg(P.sph_hot + (hot - P.n_box)) : __ldg(P.box_cull + hot);
         const float rp = packet_radius(c.w, sph, grow, pad1, pad2);
         // mode 1: the warp's cone and fan plane; 2: no cone (only near points);
         // ball_r > 0: plus the ball around the apex that holds the warp's near points
-        const bool pass = sel && ((mode == 1 && cone_pass<true>(cone, c, rp)) ||
-                                  (ball_r > 0.0f && ball_pass(cone.apex, ball_r, c, rp)));
+        bool pass = sel && ((mode == 1 && cone_pass<true>(cone, c, rp)) ||
+                            (ball_r > 0.0f && ball_pass(cone.apex, ball_r, c, rp)));
+        // more_cones (per-warp shared memory, 16 floats each): the warp's hit points in clusters, one cone per cluster
+        for (int i = 0; i < n_more; ++i) {                        // warp-uniform; 0 for most warps
+            const float* m = more_cones + 16 * i;
+            Cone k2;
+            k2.apex = cone.apex;
+            k2.axis = mk(m[0], m[1], m[2]); k2.s = m[3]; k2.c2 = m[4]; k2.reach = m[5];
+            k2.nrm = mk(m[6], m[7], m[8]); k2.hw = m[9];
+            pass = pass || (sel && cone_pass<true>(k2, c, rp));
+        }
         if (COUNT) cnt.packet_tests += sel;
         unsigned mask = __ballot_sync(kFull, pass);
         while (mask) {
@@ -255,6 +280,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
     }
     BlockShared* bs = reinterpret_cast<BlockShared*>(smem_f4 + off4);
     uint32_t* __restrict__ list_b = P.blist + (size_t)blockIdx.x * P.blist_stride;    // shadow candidates: hot index | lit-light mask << 28
+    const int rec_cap = SMEM ? 0 : P.brec_cap;                                         // ... and the bounding records of the first rec_cap
+    float4* __restrict__ rec_b = rec_cap > 0 ? P.brec + (size_t)blockIdx.x * P.brec_cap : nullptr;
     if (threadIdx.x == 0) { bs->count_a = 0u; bs->count_b[0] = 0u; bs->count_b[1] = 0u; }
     __syncthreads();
 
@@ -518,8 +545,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                 // every thread holds the same `on`, balls and cones (all read from shared memory): CTA-uniform.  The list
                 // cannot overflow: one entry per object at most, and the CTA's slice holds n_hot entries.
                 if (any_b) {
-                    if (P.n_groups > 0) block_filter_groups<COUNT, kShadowBatch>(P, w, bs, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
-                    else block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt);
+                    if (P.n_groups > 0) block_filter_groups<COUNT, kShadowBatch>(P, w, bs, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt, rec_b, rec_cap);
+                    else block_filter<SMEM, COUNT, kShadowBatch>(P, w, lc, on, ball, 0.0101f, pk_pad1, pk_pad2, list_b, P.blist_stride, &bs->count_b[s & 1], cnt, rec_b, rec_cap);
                 }
                 __syncthreads();                                                    // list B complete
                 const int nb = (int)bs->count_b[s & 1];
@@ -576,11 +603,79 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
                             const bool has_far = __any_sync(kFull, far_pt);
                             const float nw = warp_max_nonneg(nmax);
                             const float ball_r = nw > 0.0f ? __fmaf_rn(sqrt_approx(nw), 1.0001f, 0.0101f) : 0.0f;
-                            cone_close(wc[0], warp_max_nonneg(s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
+                            const float s2w = warp_max_nonneg(s2);
+                            int n_more = 0;
+                            // A warp whose 96 hit points lie at several depths (it looks past a near object at far ones) sees
+                            // them under a wide angle from the light: one cone around all of them meets hundreds of the
+                            // block's candidates, and each costs a per-ray test (blocks holding such warps took 600 us at 64k
+                            // objects against a median of 85 and set the kernel's tail).  Such a warp puts its hit points in up
+                            // to kClusters clusters -- a leader's direction from the light and everything within kSplitCos of
+                            // it, the last cluster takes what is left -- and a list entry must meet one of the clusters' cones.
+                            if (nb >= kSplitMinList && has_far && P.split_cones && (!narrow || s2w > kSplitSin2)) {
+                                bool todo[kShadowBatch];
+#pragma unroll
+                                for (int q = 0; q < kShadowBatch; ++q) todo[q] = sh[q] && !nq[q];
+                                int n_cl = 0;
+#pragma unroll 1
+                                for (int round = 0; round < kClusters; ++round) {
+                                    const unsigned r0 = __ballot_sync(kFull, todo[0]), r1 = __ballot_sync(kFull, todo[1]), r2 = __ballot_sync(kFull, todo[2]);
+                                    if ((r0 | r1 | r2) == 0u) break;
+                                    const int ql = r0 ? 0 : (r1 ? 1 : 2);
+                                    const int lead = __ffs(r0 ? r0 : (r1 ? r1 : r2)) - 1;
+                                    const V3 us = ql == 0 ? uu[0] : (ql == 1 ? uu[1] : uu[2]);
+                                    const V3 lu = mk(__shfl_sync(kFull, us.x, lead), __shfl_sync(kFull, us.y, lead), __shfl_sync(kFull, us.z, lead));
+                                    const bool last = round == kClusters - 1;
+                                    bool in_g[kShadowBatch];
+                                    V3 gs = mk(0.0f, 0.0f, 0.0f);
+#pragma unroll
+                                    for (int q = 0; q < kShadowBatch; ++q) {
+                                        in_g[q] = todo[q] && (last || dot3(uu[q], lu) >= kSplitCos);
+                                        if (in_g[q]) gs = gs + uu[q];
+                                        todo[q] = todo[q] && !in_g[q];
+                                    }
+#pragma unroll
+                                    for (int off = 16; off > 0; off >>= 1) {
+                                        gs.x += __shfl_xor_sync(kFull, gs.x, off);
+                                        gs.y += __shfl_xor_sync(kFull, gs.y, off);
+                                        gs.z += __shfl_xor_sync(kFull, gs.z, off);
+                                    }
+                                    Cone gc;
+                                    gc.apex = lpk;
+                                    gc.axis = normalize3(gs);
+                                    float g_s2 = 0.0f, g_l = 0.0f, g_h = 0.0f;
+                                    bool g_in = true;
+#pragma unroll
+                                    for (int q = 0; q < kShadowBatch; ++q) {
+                                        const V3 x = cross3(gc.axis, uu[q]);
+                                        if (in_g[q]) {
+                                            g_s2 = fmaxf(g_s2, fminf(__fmaf_rn(x.x, x.x, __fmaf_rn(x.y, x.y, __fmul_rn(x.z, x.z))), 1.0f));
+                                            g_l = fmaxf(g_l, ll[q]);
+                                            g_in = g_in && dot3(gc.axis, uu[q]) >= kConeMinCos;
+                                            g_h = fmaxf(g_h, fabsf(dot3(wn, sd3[q])));
+                                        }
+                                    }
+                                    cone_close(gc, warp_max_nonneg(g_s2), __fmaf_rn(sqrt_approx(warp_max_nonneg(g_l)), 1.0001f, 0.0101f));
+                                    if (!__all_sync(kFull, g_in)) cone_open(gc);
+                                    cone_fan(gc, wn, P.fan ? warp_max_nonneg(g_h < 1e30f ? g_h : 1e30f) : 3e38f, pk_pad1);
+                                    if (n_cl == 0) {
+                                        wc[0] = gc;
+                                    } else if (lane == 0) {
+                                        float* m = w.queue + 16 * (n_cl - 1);
+                                        m[0] = gc.axis.x; m[1] = gc.axis.y; m[2] = gc.axis.z; m[3] = gc.s; m[4] = gc.c2; m[5] = gc.reach;
+                                        m[6] = gc.nrm.x; m[7] = gc.nrm.y; m[8] = gc.nrm.z; m[9] = gc.hw;
+                                    }
+                                    ++n_cl;
+                                }
+                                __syncwarp();
+                                n_more = n_cl - 1;
+                            } else {
+                            cone_close(wc[0], s2w, __fmaf_rn(sqrt_approx(warp_max_nonneg(lmax)), 1.0001f, 0.0101f));
                             if (!narrow) cone_open(wc[0]);                                // reach and fan plane only
                             cone_fan(wc[0], wn, P.fan ? warp_max_nonneg(hmax < 1e30f ? hmax : 1e30f) : 3e38f, pk_pad1);
+                            }
                             int unused[kShadowBatch] = {-1, -1, -1};
-                            list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, has_far ? 1 : 2, ball_r, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt);
+                            list_trace<SMEM, COUNT, true>(P, w, list_b, nb, 1u << k, wc, has_far ? 1 : 2, ball_r, 0.0101f, 1.0f, pk_pad1, pk_pad2, false, so3, sd3, sbk, unused, cnt, rec_b, rec_cap, w.queue, n_more);
+                            __syncwarp();
 #pragma unroll
                             for (int q = 0; q < kShadowBatch; ++q) {
                                 if (k == 0) rsb[q][0] = sbk[q]; else if (k == 1) rsb[q][1] = sbk[q]; else rsb[q][2] = sbk[q];

@@ -657,6 +657,12 @@ def test_object_groups_change_nothing(tracer, n, w, h, depth):
     assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
     assert st_on["shaded_lights"] == st_off["shaded_lights"]
     assert 0 < st_on["packet_tests"] < st_off["packet_tests"]
+    # bit 9: one shadow cone per warp and light (no cone per cluster of hit points for warps that see several depths)
+    one, st_one = tracer.render(sc, cam, w, h, want_stats=True, no_cull=512)
+    assert np.array_equal(on, one) and np.array_equal(on, tracer.render(sc, cam, w, h, no_cull=512 | 256))
+    assert st_one["rays"] == st_on["rays"] and st_one["shaded_lights"] == st_on["shaded_lights"]
+    if n >= 4096 and depth == 0:
+        assert st_on["candidates"] < st_one["candidates"]
     # bands through the grouped filter
     canvas = np.empty_like(on)
     edges = [0, 37, 90, h]

@@ -10,5 +10,7 @@ d=[json.loads(l) for l in open("$O/${T}_bench.json") if l.startswith("{")][0]
 print("default ms", d["ms_per_step"], "e2e", d["e2e"]["ms_per_step"])
 for k,v in d["scaled"].items():
     if k=="note": continue
-    print(k, "shipped", v["shipped"]["kernel_ms"], v["shipped"]["frac_of_fp32_peak"], "nocull", v["every_slab_test_no_cull_1"]["kernel_ms"], v["every_slab_test_no_cull_1"]["frac_of_fp32_peak"], "e2e", v["e2e"])
+    nc = v.get("every_slab_test_no_cull_1")
+    print(k, "shipped %.4f ms frac %.3f" % (v["shipped"]["kernel_ms"], v["shipped"]["frac_of_fp32_peak"]),
+          ("nocull %.3f ms frac %.3f" % (nc["kernel_ms"], nc["frac_of_fp32_peak"])) if nc else "", "e2e %.4f ms (pageable %.4f)" % (v["e2e"]["ms_per_step"], v["e2e"]["ms_per_step_pageable_objects"]), v["e2e"]["frame_equals_device_frame"])
 PY
