@@ -669,3 +669,21 @@ def test_object_groups_change_nothing(tracer, n, w, h, depth):
     for y0, y1 in zip(edges[:-1], edges[1:]):
         canvas[y0:y1] = tracer.render(sc, cam, w, h, y0=y0, y1=y1, band_only=True, no_cull=16)
     assert np.array_equal(canvas, on)
+
+
+@pytest.mark.gpu
+def test_object_groups_on_a_scene_larger_than_one_sort_wave(tracer):
+    """400 000 objects: the group kernel's grid is capped at the resident CTAs, so every CTA sorts a chunk of more
+    than 1024 entries (several 256-entry rows per radix pass).  Same frame with the groups off, and against the
+    oracle on a pixel subset."""
+    sc, cam = rt.scaled_scene(400000, max_depth=0), rt.builtin_camera(0.0)
+    w, h = 320, 180
+    on, st_on = tracer.render(sc, cam, w, h, want_stats=True)
+    off, st_off = tracer.render(sc, cam, w, h, want_stats=True, no_cull=256)
+    assert np.array_equal(on, off)
+    assert st_on["rays"] == st_off["rays"] and st_on["hit_nodes"] == st_off["hit_nodes"]
+    assert 0 < st_on["packet_tests"] < st_off["packet_tests"] // 8
+    rng = np.random.default_rng(7)
+    pix = np.stack([rng.integers(0, w, 256), rng.integers(0, h, 256)], axis=1).astype(np.int32)
+    ref = ob.render(sc, cam, w, h, pixels=pix)
+    assert_parity(on[pix[:, 1], pix[:, 0]], ref, "400k objects subset")
