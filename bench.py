@@ -52,7 +52,8 @@ WORKLOADS = {
     # name: (scene kind, n_objects, width, height, spp, depth)
     "builtin_1080p_d4": ("builtin", 5, 1920, 1080, 1, 4),
     "builtin_1080p_d0": ("builtin", 5, 1920, 1080, 1, 0),
-    "builtin_720p_d0": ("builtin", 5, 1280, 720, 1, 0),
+    "builtin_720p_d0": ("builtin", 5, 1280, 720, 1, 0),     # BASELINE config 1 (the reference's window, shader as shipped)
+    "builtin_720p_d4": ("builtin", 5, 1280, 720, 1, 4),
     "builtin_4k_spp16_d4": ("builtin", 5, 3840, 2160, 16, 4),
     "scaled_1k_1080p_d0": ("scaled", 1024, 1920, 1080, 1, 0),
     "scaled_4k_1080p_d0": ("scaled", 4096, 1920, 1080, 1, 0),

@@ -8,8 +8,10 @@
  * the whole block (primary rays: around the block's corner rays, glsl:377-392; shadow rays: per lit
  * light, around the block's hit points seen from the light, glsl:808-809) and append the objects that
  * meet it to a list in shared memory.  Each warp then runs its own cone test and the per-ray tests
- * (candidate_test) over that list only.  Every object is still tested for every block -- no hierarchy
- * over the scene, no sorting -- but the pass over the N objects is paid once per 8 work items.
+ * (candidate_test) over that list only.  Below RT_GROUPS_MIN_OBJECTS every object is tested for every block
+ * (the pass over the N objects is paid once per 8 work items); above, the pass asks the bounding spheres of
+ * groups of 32 neighbouring objects first (rt_groups.cu, block_filter_groups) and tests only the members of
+ * the groups a cone met.
  *
  * The list is unordered (warps append concurrently); candidate_test's accept rule (smaller t, then lower
  * original object index) makes the result independent of the order, so frames stay byte-identical to

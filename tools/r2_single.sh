@@ -8,7 +8,7 @@ python -m pytest tests -m gpu -q > $O/r2_pytest_gpu.log 2>&1; tail -2 $O/r2_pyte
 python bench.py > $O/r2_bench_builtin_1080p_d4.json 2> $O/r2_bench.err; tail -2 $O/r2_bench.err
 python bench.py --impl reference --steps 3 --warmup 1 > $O/r2_bench_reference_arm.json 2>> $O/r2_bench.err
 rm -f $O/r2_bench_other_workloads.jsonl
-for wl in scaled_1k_1080p_d2 scaled_16k_1080p_d2 scaled_4k_1080p_d0 scaled_16k_1080p_d0 builtin_1080p_d0 builtin_4k_spp16_d4 batch256_1024_d4; do
+for wl in scaled_1k_1080p_d2 scaled_16k_1080p_d2 scaled_4k_1080p_d0 scaled_16k_1080p_d0 scaled_64k_1080p_d0 builtin_720p_d0 builtin_720p_d4 builtin_1080p_d0 builtin_4k_spp16_d4 batch256_1024_d4; do
   python bench.py --workload $wl --steps 10 --warmup 3 --no-cpu-baseline --no-legs >> $O/r2_bench_other_workloads.jsonl 2>> $O/r2_bench.err
 done
 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-legs > $O/r2_plain.log 2>&1 && \
