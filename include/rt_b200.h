@@ -152,7 +152,7 @@ typedef struct rt_options {
                                * packet tests go object by object, not through the bounding spheres of groups of 32
                                * neighbouring objects first (built from 2048 objects up, rt_groups.cu); bit 9 = block
                                * kernel: one shadow cone per warp and light, also for a warp whose hit points lie at
-                               * several depths (otherwise up to three cones, one per cluster of hit points) */
+                               * several depths (otherwise up to twelve cones, one per cluster of hit points) */
     void* done_flag;          /* optional device pointer to a 32-bit completion word -- typically in ANOTHER GPU's memory,
                                * mapped with rt_ipc_import: done_value is stored there (system-scope release, a one-thread
                                * kernel in stream order behind the render) once every framebuffer store of the call is
