@@ -27,7 +27,7 @@ constexpr int kListCap = 2048;                   // primary candidates per block
 constexpr int kGroupCap = 1024;                  // groups tested per round of block_filter_groups
 constexpr int kSplitMinList = 128;               // root shadow rays of a warp: from this many candidates in the block's list ...
 constexpr float kSplitSin2 = 0.0025f;            // ... and a cone wider than sin 0.05 (2.9 degrees) the warp's hit points go in clusters
-constexpr float kSplitCos = 0.995f;              // a cluster: directions from the light within 5.7 degrees of its leader's
+constexpr float kSplitCos = 0.99f;               // a cluster: directions from the light within 8 degrees of its leader's (0.98 .. 0.995 measure alike)
 constexpr int kClusters = 12;                    // the last one takes what the others left
 constexpr float kBlockMinCos = 0.1f;             // light cones of a block may be wide: they only feed the list, which cannot
                                                  // overflow (list B lives in HBM / L2, one slice of n_hot entries per CTA)
