@@ -25,7 +25,7 @@
 constexpr int kBlkW = 2, kBlkH = 4;              // work items per block
 constexpr int kListCap = 2048;                   // primary candidates per block; an overflowing block falls back to packet_trace
 constexpr int kGroupCap = 1024;                  // groups tested per round of block_filter_groups
-constexpr int kSplitMinList = 128;               // root shadow rays of a warp: from this many candidates in the block's list ...
+constexpr int kSplitMinList = 64;                // root shadow rays of a warp: from this many candidates in the block's list ...
 constexpr float kSplitSin2 = 0.0025f;            // ... and a cone wider than sin 0.05 (2.9 degrees) the warp's hit points go in clusters
 constexpr float kSplitCos = 0.99f;               // a cluster: directions from the light within 8 degrees of its leader's (0.98 .. 0.995 measure alike)
 constexpr int kClusters = 12;                    // the last one takes what the others left
@@ -619,8 +619,8 @@ __global__ void __launch_bounds__(kThreads, RT_MIN_BLOCKS_CULL) render_block_ker
 #pragma unroll
                                 for (int q = 0; q < kShadowBatch; ++q) todo[q] = sh[q] && !nq[q];
                                 int n_cl = 0;
-                                // every cone costs each trip of the walk a test: one cluster per 64 list entries, 2..kClusters
-                                const int max_cl = min(kClusters, max(2, nb >> 6));
+                                // every cone costs each trip of the walk a test: one cluster per 32 list entries, 2..kClusters
+                                const int max_cl = min(kClusters, max(2, nb >> 5));
 #pragma unroll 1
                                 for (int round = 0; round < max_cl; ++round) {
                                     const unsigned r0 = __ballot_sync(kFull, todo[0]), r1 = __ballot_sync(kFull, todo[1]), r2 = __ballot_sync(kFull, todo[2]);
