@@ -10,7 +10,8 @@ reps = int(sys.argv[1]) if len(sys.argv) > 1 else 6
 bad = 0
 with rt.Raytracer(0) as r:
     for k in range(reps):
-        for n, depth, w, h in ((2100, 0, 320, 180), (5000, 1, 240, 136), (20000, 0, 320, 180), (9000, 2, 160, 90)):
+        for n, depth, w, h in ((2100, 0, 320, 180), (5000, 1, 240, 136), (20000, 0, 320, 180), (9000, 2, 160, 90),
+                               (70000, 0, 480, 270), (300, 0, 320, 180), (3000, 0, 640, 360)):
             sc = rt.scaled_scene(n, seed=0xC0FFEE00 + 977 * k + n, max_depth=depth)
             cam = rt.builtin_camera(0.37 * k + 0.11 * depth)
             a = r.render(sc, cam, w, h)
@@ -20,4 +21,4 @@ with rt.Raytracer(0) as r:
                 if d:
                     bad += 1
                     print("DIFF", k, n, depth, "mode", mode, "pixels", d)
-print("cases", reps * 4 * 5, "bad", bad)
+print("cases", reps * 7 * 5, "bad", bad)
