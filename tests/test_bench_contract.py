@@ -60,10 +60,19 @@ def test_reference_arm_uses_all_host_threads_under_torchrun():
     d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
     assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
     assert d["config"] == bench.static_config("builtin_720p_d0", bench.WORKLOADS["builtin_720p_d0"], 2)
-    if len(os.sched_getaffinity(0)) > 1:
-        one = _run(["--impl", "reference", "--steps", "1", "--warmup", "0", "--workload", "builtin_720p_d0"])
-        v1 = json.loads([l for l in one.stdout.splitlines() if l.startswith("{")][0])["value"]
-        assert d["value"] > 0.5 * v1            # not a one-thread run: same ball park as the plain launch
+    if len(os.sched_getaffinity(0)) >= 4:
+        # not a one-thread run: same ball park as the plain launch.  Two short CPU timings on a shared host: the
+        # better of two runs each, and a wide margin (a one-thread run would sit at 1 / cores)
+        def best(args, env=None):
+            vals = []
+            for _ in range(2):
+                rr = _run(args, env=env)
+                vals.append(json.loads([l for l in rr.stdout.splitlines() if l.startswith("{")][0])["value"])
+            return max(vals)
+        v1 = best(["--impl", "reference", "--steps", "1", "--warmup", "0", "--workload", "builtin_720p_d0"])
+        vt = max(d["value"], best(["--impl", "reference", "--steps", "1", "--warmup", "0", "--gpus", "2", "--workload", "builtin_720p_d0"],
+                                  env={"RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0", "OMP_NUM_THREADS": "1"}))
+        assert vt > 0.4 * v1
 
 
 def test_roofline_flops_credit_executed_work_only():
