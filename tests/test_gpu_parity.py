@@ -69,6 +69,15 @@ def test_golden_fixtures_on_gpu(tracer):
         for strict in (True, False):
             img = tracer.render(rt.builtin_scene(t, d), rt.builtin_camera(t), w, h, strict=strict)
             _check(img, npz[name], "golden %s strict=%s" % (name, strict))
+    # scaled synthetic scene: the large-scene kernels (object groups, block / per-warp kernel, bounce trees) against
+    # committed oracle frames
+    snpz = np.load(os.path.join(HERE, "golden", "golden_scaled.npz"))
+    for case in gold["scaled"]:
+        name = "n%d_d%d_w%d_h%d" % (case["objects"], case["depth"], case["width"], case["height"])
+        sc = rt.scaled_scene(case["objects"], max_depth=case["depth"])
+        for strict in (True, False):
+            img = tracer.render(sc, rt.builtin_camera(0.0), case["width"], case["height"], strict=strict)
+            _check(img, snpz[name], "golden %s strict=%s" % (name, strict))
     # strict kernel reproduces the shipped-depth golden frame hash bit for bit
     case = [c for c in gold["cases"] if c["depth"] == 0 and c["width"] == 1280][0]
     img = tracer.render(rt.builtin_scene(0.0, 0), rt.builtin_camera(0.0), 1280, 720, strict=True)
